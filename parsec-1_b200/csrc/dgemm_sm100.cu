@@ -1,0 +1,542 @@
+// FP64 tile DGEMM for sm_100a: C = alpha * op(A) * op(B) + beta * C, column-major.
+//
+// This is the kernel a `BODY [type=CUDA dyld=parsec_b200_dgemm]` task body launches on the
+// exec stream the device module hands it.  It replaces the cublasDgemm_v2 call of the
+// reference's CUDA bodies (tests/dsl/dtd/dtd_test_simple_gemm.c:197-202,
+// tests/dsl/ptg/cuda/nvlink.jdf:142, stress.jdf:135): same argument order and meaning,
+// column-major, leading dimensions in elements.
+//
+// Fast path (N,N; M%128 == N%128 == 0; K%16 == 0; 16-byte aligned operands, even lds):
+//   CTA tile 128x128, BK = 16, 256 threads = 8 warps in a 2(m) x 4(n) grid, warp tile
+//   64x32 = 8x4 DMMA.8x8x4 tiles (mma.sync.m8n8k4.f64 is the native FP64 tensor op on
+//   sm_100a; wider shapes lower to the same SASS).  Operands are staged with 16-byte
+//   cp.async into a 4-deep shared-memory ring in their *global* orientation
+//   (A: m fastest, B: k fastest), so no transpose is ever needed:
+//     - A fragment rows are permuted (DMMA tile i, fragment row g  <->  tile row 8g+i) so one
+//       thread reads 8 consecutive doubles of a k-column with four LDS.128; the row pitch
+//       BM+2 makes the quarter-warp accesses hit 8 distinct 16-byte bank groups.
+//     - B fragments are LDS.64 with pitch BK+4 (conflict free per half warp).
+//   The same row permutation makes every thread own 8 consecutive rows of 8 columns of C,
+//   so the epilogue is 16-byte loads/stores.
+// Everything else (ragged tiles, transposes, unaligned) goes through a bounds-checked
+// 64x64 DMMA kernel; it exists for the edge tiles of N % NB != 0 matrices.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "pb2_internal.h"
+#include "tma_utils.cuh"
+#include <stdlib.h>
+#include <string.h>
+
+namespace pb2 {
+
+constexpr int BM = 128, BN = 128, BK = 16;
+constexpr int STAGES = 4;
+constexpr int LDA_S = BM + 2;          // doubles; (LDA_S/2) % 8 == 1
+constexpr int LDB_S = BK + 4;          // doubles; LDB_S % 16 == 4
+constexpr int A_STAGE = BK * LDA_S;    // doubles per stage
+constexpr int B_STAGE = BN * LDB_S;
+constexpr int DGEMM_THREADS = 256;
+constexpr size_t DGEMM_SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double);
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(DGEMM_THREADS, 1)
+dgemm_nn_128x128(int M, int N, int K, double alpha, const double* __restrict__ A, int lda,
+                 const double* __restrict__ B, int ldb, double beta, double* __restrict__ C, int ldc) {
+    extern __shared__ __align__(16) double smem[];
+    double* As = smem;
+    double* Bs = smem + STAGES * A_STAGE;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int tiles_m = M / BM;
+    const int bm = blockIdx.x % tiles_m, bn = blockIdx.x / tiles_m;
+    (void)N;
+
+    const double* Ag = A + (size_t)bm * BM;
+    const double* Bg = B + (size_t)bn * BN * ldb;
+
+    auto load_stage = [&](int stage, int kt) {
+        double* as = As + stage * A_STAGE;
+        const double* ag = Ag + (size_t)kt * BK * lda;
+#pragma unroll
+        for (int i = 0; i < (BK * BM / 2) / DGEMM_THREADS; ++i) {
+            int c = tid + i * DGEMM_THREADS;
+            int kr = c / (BM / 2), mc = c % (BM / 2);
+            cp_async16(as + kr * LDA_S + mc * 2, ag + (size_t)kr * lda + mc * 2);
+        }
+        double* bs = Bs + stage * B_STAGE;
+        const double* bg = Bg + (size_t)kt * BK;
+#pragma unroll
+        for (int i = 0; i < (BN * BK / 2) / DGEMM_THREADS; ++i) {
+            int c = tid + i * DGEMM_THREADS;
+            int n = c / (BK / 2), kc = c % (BK / 2);
+            cp_async16(bs + n * LDB_S + kc * 2, bg + (size_t)n * ldb + kc * 2);
+        }
+    };
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    const int KT = K / BK;
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; ++s) {
+        if (s < KT) load_stage(s, s);
+        cp_async_commit();
+    }
+
+    for (int kt = 0; kt < KT; ++kt) {
+        cp_async_wait<STAGES - 2>();
+        __syncthreads();
+        {
+            int nk = kt + STAGES - 1;
+            if (nk < KT) load_stage(nk % STAGES, nk);
+            cp_async_commit();
+        }
+        const double* as = As + (kt % STAGES) * A_STAGE + wm * 64 + 8 * g;
+        const double* bs = Bs + (kt % STAGES) * B_STAGE + (wn * 32 + g) * LDB_S + t;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            double a[8], b[4];
+            const double* ap = as + (ks * 4 + t) * LDA_S;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                double2 v = *reinterpret_cast<const double2*>(ap + 2 * q);
+                a[2 * q] = v.x;
+                a[2 * q + 1] = v.y;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bs[j * 8 * LDB_S + ks * 4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+
+    // Epilogue: thread owns rows [8g, 8g+8) of columns 8j + 2t + e of its warp tile.
+    const size_t row0 = (size_t)bm * BM + wm * 64 + 8 * g;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const size_t col = (size_t)bn * BN + wn * 32 + 8 * j + 2 * t + e;
+            double2* cp = reinterpret_cast<double2*>(C + row0 + col * ldc);
+            if (beta == 0.0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    double2 v;
+                    v.x = alpha * acc[2 * q][j][e];
+                    v.y = alpha * acc[2 * q + 1][j][e];
+                    cp[q] = v;
+                }
+            } else {
+                double2 old[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) old[q] = cp[q];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    double2 v;
+                    v.x = alpha * acc[2 * q][j][e] + beta * old[q].x;
+                    v.y = alpha * acc[2 * q + 1][j][e] + beta * old[q].y;
+                    cp[q] = v;
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA + mbarrier warp-specialised variant (the default fast path).
+//   warps 0-7: consumers (2 x 4 grid of 64x32 warp tiles, DMMA.8x8x4), warp 8: TMA producer
+//   (warps 9-11 only exist so the producer is a whole warpgroup and can setmaxnreg.dec).
+//   Stage = A tile as 8 boxes of [16 k][16 m] + B tile as one box [128 n][16 k], both with
+//   128-byte rows and CU_TENSOR_MAP_SWIZZLE_128B, so every LDS below is bank-conflict free:
+//     A: LDS.128, quarter warp = (g&1, t) -> chunk ((g&1)^(ks&1))*4 + (q^t)      (8 distinct)
+//     B: LDS.64,  half warp    = (g&3, t) -> slot 4*(ks^(g&3)) + 2*((t>>1)^(j&1)) + (t&1) (16 distinct)
+//   B columns are permuted inside a warp tile (DMMA tile j, fragment column g <-> column
+//   16*(j>>1) + 2g + (j&1)) to make the hardware swizzle (which XORs with n&7) conflict free.
+//   There is no CTA-wide barrier in the main loop: consumers wait on full[stage], arrive on
+//   empty[stage]; the first fragments of tile kt+1 are fetched under the last DMMAs of tile kt.
+//   Out-of-range rows/columns/k are zero-filled by TMA, so any m, n, k is accepted.
+constexpr int T_STAGES = 6;
+constexpr int T_A_BYTES = BK * BM * 8;  // 16 KiB
+constexpr int T_B_BYTES = BK * BN * 8;  // 16 KiB
+constexpr int T_STAGE_BYTES = T_A_BYTES + T_B_BYTES;
+constexpr int T_CONSUMER_WARPS = 8;
+constexpr int T_THREADS = (T_CONSUMER_WARPS + 4) * 32;  // 2 consumer warpgroups + 1 producer warpgroup
+constexpr size_t T_SMEM = (size_t)T_STAGES * T_STAGE_BYTES + 1024 + 2 * T_STAGES * sizeof(uint64_t);
+
+__device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];\n" : "=d"(x), "=d"(y) : "r"(addr));
+}
+__device__ __forceinline__ double lds64(uint32_t addr) {
+    double x;
+    asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(x) : "r"(addr));
+    return x;
+}
+__device__ __forceinline__ void dmma884p(double& d0, double& d1, double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+        : "+d"(d0), "+d"(d1)
+        : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(T_THREADS, 1)
+dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
+             double alpha, double beta, double* __restrict__ C, int ldc) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase0 = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (sbase0 - raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + T_STAGES * T_STAGE_BYTES);
+    uint64_t* empty = full + T_STAGES;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tiles_m = (M + BM - 1) / BM;
+    const int bm = blockIdx.x % tiles_m, bn = blockIdx.x / tiles_m;
+    const int m0 = bm * BM, n0 = bn * BN;
+    const int KT = (K + BK - 1) / BK;
+
+    if (tid == 0) {
+        for (int s = 0; s < T_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], T_CONSUMER_WARPS);
+        }
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    __syncthreads();
+
+    if (warp >= T_CONSUMER_WARPS) {
+        // producer warpgroup: hand its registers to the consumers (168*384 = 232*256 + 40*128)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n" ::);
+        if (warp == T_CONSUMER_WARPS && lane == 0) {
+            tma_prefetch_desc(&mapA);
+            tma_prefetch_desc(&mapB);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = 0; kt < KT; ++kt) {
+                if (kt >= T_STAGES) mbar_wait(&empty[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * T_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full[stage], T_STAGE_BYTES);
+#pragma unroll
+                for (int b = 0; b < BM / 16; ++b) tma_load_2d(sa + b * 2048, &mapA, m0 + 16 * b, kt * BK, &full[stage]);
+                tma_load_2d(sa + T_A_BYTES, &mapB, kt * BK, n0, &full[stage]);
+                if (++stage == T_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+        return;
+    }
+
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;\n" ::);
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;
+
+    // per-thread shared-memory offsets (bytes, relative to the stage base)
+    const uint32_t a_thread = (uint32_t)((4 * wm + (g >> 1)) * 2048 + t * 128);
+    uint32_t a_off[2][4];
+#pragma unroll
+    for (int p = 0; p < 2; ++p)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a_off[p][q] = (uint32_t)(((((g & 1) ^ p) * 4) + (q ^ t)) * 16);
+    const uint32_t b_thread = (uint32_t)(T_A_BYTES + (32 * wn + 2 * g) * 128 + (t & 1) * 8);
+    uint32_t b_x[4], b_par[2];
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) b_x[ks] = (uint32_t)((ks ^ (g & 3)) * 32);
+    b_par[0] = (uint32_t)((t >> 1) * 16);
+    b_par[1] = (uint32_t)(((t >> 1) ^ 1) * 16);
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    double a[2][8], b[2][4];
+    auto load_frags = [&](int buf, uint32_t sb, int ks) {
+        const uint32_t ab = sb + a_thread + ks * 512;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) lds128(a[buf][2 * q], a[buf][2 * q + 1], ab + a_off[ks & 1][q]);
+        const uint32_t bb = sb + b_thread + b_x[ks];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[buf][j] = lds64(bb + (16 * (j >> 1) + (j & 1)) * 128 + b_par[j & 1]);
+    };
+
+    if (KT > 0) {
+        int stage = 0;
+        uint32_t phase = 0;
+        mbar_wait(&full[0], 0);
+        load_frags(0, sbase0, 0);
+        for (int kt = 0; kt < KT; ++kt) {
+            const uint32_t sb = sbase0 + stage * T_STAGE_BYTES;
+            int nstage = stage + 1;
+            uint32_t nphase = phase;
+            if (nstage == T_STAGES) {
+                nstage = 0;
+                nphase ^= 1;
+            }
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                if (ks < 3) {
+                    load_frags((ks + 1) & 1, sb, ks + 1);
+                } else if (kt + 1 < KT) {
+                    mbar_wait(&full[nstage], nphase);
+                    load_frags(0, sbase0 + nstage * T_STAGE_BYTES, 0);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dmma884p(acc[i][j][0], acc[i][j][1], a[ks & 1][i], b[ks & 1][j]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[stage]);
+            stage = nstage;
+            phase = nphase;
+        }
+    }
+
+    // Epilogue.  acc[i][j][e]: row = m0 + 64wm + 8g + i, col = n0 + 32wn + 16(j>>1) + 4t + 2e + (j&1).
+    const int row0 = m0 + wm * 64 + 8 * g;
+    const bool rows_full = (row0 + 8 <= M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+            if (col >= N) continue;
+            double* cptr = C + (size_t)row0 + (size_t)col * ldc;
+            if (rows_full) {
+                double2* cp = reinterpret_cast<double2*>(cptr);
+                if (beta == 0.0) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        double2 v;
+                        v.x = alpha * acc[2 * q][j][e];
+                        v.y = alpha * acc[2 * q + 1][j][e];
+                        cp[q] = v;
+                    }
+                } else {
+                    double2 old[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) old[q] = cp[q];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        double2 v;
+                        v.x = alpha * acc[2 * q][j][e] + beta * old[q].x;
+                        v.y = alpha * acc[2 * q + 1][j][e] + beta * old[q].y;
+                        cp[q] = v;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (row0 + i < M) {
+                        double r = alpha * acc[i][j][e];
+                        if (beta != 0.0) r += beta * cptr[i];
+                        cptr[i] = r;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// General kernel: any M, N, K, any transposes, any alignment.  CTA tile 64x64, BK = 16,
+// 128 threads = 4 warps (2x2), warp tile 32x32 = 4x4 DMMA tiles, predicated scalar staging.
+constexpr int GM = 64, GN = 64, GK = 16;
+constexpr int LDGA = GM + 4;  // As[k][m]
+constexpr int LDGB = GK + 4;  // Bs[n][k]
+
+__global__ void __launch_bounds__(128)
+dgemm_generic_64x64(int transa, int transb, int M, int N, int K, double alpha,
+                    const double* __restrict__ A, int lda, const double* __restrict__ B, int ldb,
+                    double beta, double* __restrict__ C, int ldc) {
+    __shared__ double As[GK * LDGA];
+    __shared__ double Bs[GN * LDGB];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int m0 = blockIdx.x * GM, n0 = blockIdx.y * GN;
+
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    for (int k0 = 0; k0 < K; k0 += GK) {
+        // stage A: 64x16 elements, 128 threads -> 8 each; m fastest across threads when !transa
+        for (int idx = tid; idx < GM * GK; idx += 128) {
+            int m, k;
+            if (!transa) { m = idx % GM; k = idx / GM; } else { k = idx % GK; m = idx / GK; }
+            int gm = m0 + m, gk = k0 + k;
+            double v = 0.0;
+            if (gm < M && gk < K) v = transa ? A[(size_t)gk + (size_t)gm * lda] : A[(size_t)gm + (size_t)gk * lda];
+            As[k * LDGA + m] = v;
+        }
+        for (int idx = tid; idx < GN * GK; idx += 128) {
+            int n, k;
+            if (!transb) { k = idx % GK; n = idx / GK; } else { n = idx % GN; k = idx / GN; }
+            int gn = n0 + n, gk = k0 + k;
+            double v = 0.0;
+            if (gn < N && gk < K) v = transb ? B[(size_t)gn + (size_t)gk * ldb] : B[(size_t)gk + (size_t)gn * ldb];
+            Bs[n * LDGB + k] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int ks = 0; ks < GK / 4; ++ks) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[(ks * 4 + t) * LDGA + wm * 32 + 8 * i + g];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[(wn * 32 + 8 * j + g) * LDGB + ks * 4 + t];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                int row = m0 + wm * 32 + 8 * i + g;
+                int col = n0 + wn * 32 + 8 * j + 2 * t + e;
+                if (row < M && col < N) {
+                    double* p = C + (size_t)row + (size_t)col * ldc;
+                    double r = alpha * acc[i][j][e];
+                    if (beta != 0.0) r += beta * *p;
+                    *p = r;
+                }
+            }
+}
+
+static bool g_attr_set[64] = {false};
+
+static int ensure_smem_attr() {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return PB2_ERR_CUDA;
+    if (dev < 64 && g_attr_set[dev]) return PB2_SUCCESS;
+    e = cudaFuncSetAttribute(dgemm_nn_128x128, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DGEMM_SMEM);
+    if (e != cudaSuccess) return PB2_ERR_CUDA;
+    e = cudaFuncSetAttribute(dgemm_nn_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e != cudaSuccess) return PB2_ERR_CUDA;
+    if (dev < 64) g_attr_set[dev] = true;
+    return PB2_SUCCESS;
+}
+
+// 0 = TMA/mbarrier kernel (default), 1 = cp.async kernel (PB2_DGEMM_IMPL=cpasync; kept for A/B runs)
+static int dgemm_impl() {
+    static int impl = -1;
+    if (impl < 0) {
+        const char* e = getenv("PB2_DGEMM_IMPL");
+        impl = (e && !strcmp(e, "cpasync")) ? 1 : 0;
+    }
+    return impl;
+}
+
+// Tensor maps depend only on (base, dims, ld); tile pointers recur (HBM cache slots), so keep a
+// small direct-mapped cache per thread.
+struct TmapKey {
+    const void* p;
+    int d0, d1, ld, kind;
+};
+struct TmapEntry {
+    TmapKey k;
+    CUtensorMap m;
+    bool valid;
+};
+static int get_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int kind) {
+    static thread_local TmapEntry cache[512];
+    uintptr_t h = ((uintptr_t)p >> 9) * 0x9E3779B97F4A7C15ull + (uintptr_t)(d0 * 31 + d1 * 17 + ld * 7 + kind);
+    TmapEntry& e = cache[(h >> 20) & 511];
+    if (e.valid && e.k.p == p && e.k.d0 == d0 && e.k.d1 == d1 && e.k.ld == ld && e.k.kind == kind) {
+        *out = e.m;
+        return 0;
+    }
+    int rc = kind == 0 ? encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, p, d0, d1, ld, 16, BK,
+                                        CU_TENSOR_MAP_SWIZZLE_128B)
+                       : encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, p, d0, d1, ld, BK, BN,
+                                        CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) {
+        e.valid = false;
+        return rc;
+    }
+    e.k = {p, d0, d1, ld, kind};
+    e.valid = true;
+    *out = e.m;
+    return 0;
+}
+
+static inline int trans_of(char c) {
+    if (c == 'N' || c == 'n') return 0;
+    if (c == 'T' || c == 't' || c == 'C' || c == 'c') return 1;
+    return -1;
+}
+
+}  // namespace pb2
+
+extern "C" int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, int k, double alpha,
+                                        const double* A, int lda, const double* B, int ldb, double beta,
+                                        double* C, int ldc, void* stream) {
+    using namespace pb2;
+    const int ta = trans_of(transa), tb = trans_of(transb);
+    if (ta < 0 || tb < 0 || m < 0 || n < 0 || k < 0) return PB2_ERR_BAD_PARAM;
+    if (lda < (ta ? (k > 1 ? k : 1) : (m > 1 ? m : 1)) || ldb < (tb ? (n > 1 ? n : 1) : (k > 1 ? k : 1)) ||
+        ldc < (m > 1 ? m : 1))
+        return PB2_ERR_BAD_PARAM;
+    if (m == 0 || n == 0) return PB2_SUCCESS;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool aligned = (((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0 && !(lda & 1) && !(ldb & 1) &&
+                         !(ldc & 1);
+    if (!ta && !tb && aligned && k > 0 && dgemm_impl() == 0) {
+        int rc = ensure_smem_attr();
+        if (rc != PB2_SUCCESS) return rc;
+        CUtensorMap ma, mb;
+        if (get_tmap(&ma, A, m, k, lda, 0) || get_tmap(&mb, B, k, n, ldb, 1)) return PB2_ERR_CUDA;
+        dim3 grid(((m + BM - 1) / BM) * ((n + BN - 1) / BN));
+        dgemm_nn_tma<<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+    } else if (!ta && !tb && aligned && k > 0 && m % BM == 0 && n % BN == 0 && k % BK == 0) {
+        int rc = ensure_smem_attr();
+        if (rc != PB2_SUCCESS) return rc;
+        dim3 grid((m / BM) * (n / BN));
+        dgemm_nn_128x128<<<grid, DGEMM_THREADS, DGEMM_SMEM, st>>>(m, n, k, alpha, A, lda, B, ldb, beta, C, ldc);
+    } else {
+        dim3 grid((m + GM - 1) / GM, (n + GN - 1) / GN);
+        dgemm_generic_64x64<<<grid, 128, 0, st>>>(ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc);
+    }
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+// dyld= lookup tries "<fn>_sm100" first and then "<fn>" (device_cuda_module.c:175-240).
+extern "C" int parsec_b200_dgemm(char transa, char transb, int m, int n, int k, double alpha, const double* A,
+                                  int lda, const double* B, int ldb, double beta, double* C, int ldc, void* stream) {
+    return parsec_b200_dgemm_sm100(transa, transb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+}
