@@ -1,0 +1,145 @@
+/*
+ * CPU oracle for the PaRSEC CUDA-device tiled-GEMM hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: it may be imported,
+ * linked or executed only by tests/, by __graft_entry__.smoke() and by bench.py's cpu_baseline /
+ * --impl reference legs, always as the checker or the CPU baseline, never as the thing shipped.
+ *
+ * Each function restates, in plain C, what the reference does on this path; the file:line it
+ * follows (relative to /root/reference) is cited next to it in pb2_oracle.c.
+ *
+ * Parity pinning (see DESIGN.md "Oracle"):
+ *   - zone allocator: pinned against the reference's own parsec/utils/zone_malloc.c compiled from
+ *     where it lies into oracle/_ref/ (tests/test_oracle_ref.py, golden tests/golden/zone_trace.json);
+ *   - block-cyclic mapping, input generator, coherency/version state machine: pinned against the
+ *     reference's golden values recorded in SURVEY.md (task counts 512+64+64 at N=2048/NB=256, final
+ *     C-tile version == KT) and the worked sequence of SURVEY.md Appendix C;
+ *   - tile GEMM arithmetic: the reference ships no GEMM (its bodies call cuBLAS / an un-vendored
+ *     CBLAS), so the arithmetic is "parity unpinned" at the BLAS boundary; the oracle follows the
+ *     column-major convention of every CUDA body in the tree.
+ */
+#ifndef PB2_ORACLE_H
+#define PB2_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- input generator ------------------------------------------------------------------- */
+uint64_t orc_rnd64_jump(uint64_t n, uint64_t seed);
+void orc_init_tile(double* data, int m, int n, int mb, int nb, int M, int ld, unsigned seed);
+
+/* ---- 2D block-cyclic tiled matrix ------------------------------------------------------ */
+typedef struct orc_bc_s {
+    int mb, nb, lm, ln, i, j, m, n;
+    int mt, nt, lmt, lnt, llm, lln, bsiz;
+    int P, Q, kp, kq, ip, jq, rrank, crank, myrank;
+    int nb_elem_r, nb_elem_c, nb_local_tiles;
+} orc_bc_t;
+
+void orc_bc_init(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q,
+                 int kp, int kq, int ip, int jq);
+int orc_bc_rank_of(const orc_bc_t* dc, int m, int n);
+int orc_bc_position(const orc_bc_t* dc, int m, int n);
+uint64_t orc_bc_key(const orc_bc_t* dc, int m, int n);
+void orc_bc_key2coords(const orc_bc_t* dc, uint64_t key, int* m, int* n);
+/* fill every locally stored tile of a PARSEC_MATRIX_TILE-storage matrix (mat holds nb_local_tiles*bsiz doubles) */
+void orc_bc_fill(const orc_bc_t* dc, double* mat, unsigned seed, int nthreads);
+
+/* ---- tile GEMM and the tiled GEMM DAG --------------------------------------------------- */
+void orc_dgemm_tile(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
+                    double beta, double* C, int ldc);
+
+typedef struct orc_counts_s {
+    int64_t gemm, read_a, read_b;
+} orc_counts_t;
+
+/* C(M x N) += A(M x K) * B(K x N); single rank (P = Q = 1), tile storage, tiles mb x kb, kb x nb, mb x nb.
+ * c_versions (mt*nt, column-major over tiles) receives the final host-copy version of every C tile. */
+int orc_tiled_dgemm(int M, int N, int K, int mb, int nb, int kb, const double* A, const double* B, double* C,
+                    int nthreads, orc_counts_t* counts, uint32_t* c_versions);
+
+/* BF16-in / FP32-accumulate tile GEMM (config 5): A, B are bf16 bit patterns, C is fp32. */
+void orc_gemm_tile_bf16(int mb, int nb, int kb, float alpha, const uint16_t* A, int lda, const uint16_t* B, int ldb,
+                        float beta, float* C, int ldc);
+uint16_t orc_f32_to_bf16_rn(float x);
+
+/* ||C - Cref||inf / (||A||inf ||B||inf N eps) with matrix inf-norms over the tile-stored operands. */
+double orc_matrix_inf_norm_tiled(const orc_bc_t* dc, const double* mat);
+
+/* ---- data copies: coherency / version state machine ------------------------------------ */
+#define ORC_MAX_DEV 10
+enum { ORC_COH_INVALID = 0, ORC_COH_OWNED = 1, ORC_COH_EXCLUSIVE = 2, ORC_COH_SHARED = 4 };
+enum { ORC_XFER_NONE = 0, ORC_XFER_UNDER = 1, ORC_XFER_COMPLETE = 2 };
+enum { ORC_ACCESS_READ = 1, ORC_ACCESS_WRITE = 2, ORC_ACCESS_RW = 3 };
+
+typedef struct orc_copy_s {
+    uint8_t present, coherency, transfer_status;
+    int32_t readers;
+    uint32_t version;
+} orc_copy_t;
+
+typedef struct orc_data_s {
+    uint64_t key;
+    int8_t owner_device, preferred_device;
+    int nb_devices;
+    orc_copy_t copies[ORC_MAX_DEV];
+} orc_data_t;
+
+void orc_data_create(orc_data_t* d, uint64_t key, int nb_devices);
+int orc_data_start_transfer_ownership(orc_data_t* d, int device, int access);
+void orc_data_end_transfer_ownership(orc_data_t* d, int device, int access);
+/* device-module steps on one flow of one task; return value documented in the .c file */
+int orc_gpu_reserve(orc_data_t* d, int device);
+int orc_gpu_stage_in(orc_data_t* d, int device, int access);
+void orc_gpu_complete_push(orc_data_t* d, int device, int access);
+int orc_gpu_pop(orc_data_t* d, int device, int access, int pushout);
+int orc_gpu_epilog(orc_data_t* d, int device, int access, int pushout);
+void orc_complete_hook(orc_data_t* d, int access);
+void orc_gpu_w2r_start(orc_data_t* d, int device);
+int orc_gpu_w2r_complete(orc_data_t* d, int device);
+void orc_gpu_evict(orc_data_t* d, int device);
+
+/* Event record shared (same layout) with the product's trace, see include/parsec_b200.h pb2_event_t */
+typedef struct orc_event_s {
+    uint32_t dc;      /* 0 = A, 1 = B, 2 = C */
+    uint32_t key;     /* tile key n*lmt + m */
+    int32_t kind;     /* ORC_EV_* */
+    int32_t k;        /* k index of the GEMM task (or -1) */
+    uint32_t gpu_version, cpu_version;
+    uint8_t gpu_coh, cpu_coh;
+    int8_t owner_device;
+    int8_t transfer; /* 1 if this step scheduled a copy (H2D on stage-in, D2H on pop) */
+} orc_event_t;
+enum {
+    ORC_EV_RESERVE = 1,
+    ORC_EV_STAGE_IN = 2,
+    ORC_EV_PUSH_DONE = 3,
+    ORC_EV_POP = 4,
+    ORC_EV_EPILOG = 5,
+    ORC_EV_COMPLETE = 6,
+    ORC_EV_W2R = 7,
+    ORC_EV_EVICT = 8
+};
+
+/* Replays the in-core (no eviction) GEMM DAG of MT x NT x KT tasks on one GPU (device index `device`,
+ * the reference numbers the first GPU 2) in k-outer order and writes every per-flow event.  Returns the number
+ * of events (call with events == NULL to size the buffer). */
+int64_t orc_trace_tiled_gemm(int MT, int NT, int KT, int device, orc_event_t* events, int64_t max_events);
+
+/* ---- zone allocator (first fit over fixed-size units) ----------------------------------- */
+typedef struct orc_zone_s orc_zone_t;
+orc_zone_t* orc_zone_init(int max_segment, size_t unit_size);
+void orc_zone_fini(orc_zone_t* z);
+/* returns the byte offset from the zone base, or -1 when no segment fits */
+int64_t orc_zone_malloc(orc_zone_t* z, size_t size);
+int orc_zone_free(orc_zone_t* z, int64_t offset);
+size_t orc_zone_in_use(const orc_zone_t* z);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,24 @@
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _built():
+    """Make sure the oracle (and, where a compiler is present, the C-ABI library) exist."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle.so")):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+    lib = os.path.join(ROOT, "parsec-1_b200", "libparsec_b200.so")
+    if not os.path.exists(lib) and os.path.exists("/usr/local/cuda/bin/nvcc"):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "parsec-1_b200"), "-j8"])
+    yield

@@ -1,0 +1,77 @@
+"""Regenerates the golden vectors from the REFERENCE's own code.
+
+Run in the build container only (needs /root/reference): `make -C oracle ref` compiles the reference's
+parsec/utils/zone_malloc.c and parsec/data_dist/matrix/grid_2Dcyclic.c from where they lie into
+oracle/_ref/libparsec_refbits.so; this script drives that library and records its outputs:
+
+  zone_trace.json  seeded malloc/free sequences -> offsets returned by the reference allocator
+  grid.json        (rank, P, Q, kp, kq, ip, jq) -> (rrank, crank) from parsec_grid_2Dcyclic_init
+
+The oracle restatement (oracle/pb2_oracle.c) and the product's HBM heap are then checked against these
+files on any machine.
+"""
+import ctypes as C
+import json
+import os
+import random
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+ref = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libparsec_refbits.so"))
+ref.zone_malloc_init.restype = C.c_void_p
+ref.zone_malloc_init.argtypes = [C.c_void_p, C.c_int, C.c_size_t]
+ref.zone_malloc.restype = C.c_void_p
+ref.zone_malloc.argtypes = [C.c_void_p, C.c_size_t]
+ref.zone_free.argtypes = [C.c_void_p, C.c_void_p]
+ref.zone_in_use.restype = C.c_size_t
+ref.zone_in_use.argtypes = [C.c_void_p]
+BASE = 1 << 40  # fake device base address; the allocator only does arithmetic on it
+
+
+def zone_case(seed, nseg, unit, nops, sizes):
+    rng = random.Random(seed)
+    z = ref.zone_malloc_init(BASE, nseg, unit)
+    live, ops = [], []
+    for _ in range(nops):
+        if live and (rng.random() < 0.45 or len(live) > nseg):
+            i = rng.randrange(len(live))
+            off = live.pop(i)
+            ref.zone_free(z, BASE + off)
+            ops.append(["free", off, int(ref.zone_in_use(z))])
+        else:
+            sz = rng.choice(sizes)
+            p = ref.zone_malloc(z, sz)
+            off = -1 if not p else p - BASE
+            if off >= 0:
+                live.append(off)
+            ops.append(["malloc", sz, off, int(ref.zone_in_use(z))])
+    return {"seed": seed, "nseg": nseg, "unit": unit, "ops": ops}
+
+
+def main():
+    KiB = 1024
+    cases = [
+        zone_case(1, 64, 512 * KiB, 400, [512 * KiB, 8 * 1024 * KiB, 2 * 1024 * KiB]),  # 512K/2M/8M tiles
+        zone_case(2, 200, 512 * KiB, 1500, [8 * 1024 * KiB]),                             # NB=1024 fp64 only
+        zone_case(3, 97, 4096, 2000, [1, 4096, 4097, 10000, 40000, 65536]),              # ragged sizes
+        zone_case(4, 16, 512 * KiB, 300, [32 * 1024 * KiB, 8 * 1024 * KiB]),              # mostly failing
+    ]
+    json.dump(cases, open(os.path.join(HERE, "zone_trace.json"), "w"))
+
+    class Grid(C.Structure):
+        _fields_ = [(n, C.c_int) for n in "rank rows cols ip jq krows kcols crank rrank rloc cloc vp_p vp_q".split()]
+
+    grids = []
+    for (P, Q) in [(1, 1), (1, 2), (2, 2), (2, 4), (4, 2), (3, 5)]:
+        for (kp, kq, ip, jq) in [(1, 1, 0, 0), (2, 3, 0, 0), (1, 1, 1, 1 % Q)]:
+            for rank in range(P * Q):
+                g = Grid()
+                ref.parsec_grid_2Dcyclic_init(C.byref(g), rank, P, Q, kp, kq, ip % P, jq % Q)
+                grids.append({"rank": rank, "P": P, "Q": Q, "kp": kp, "kq": kq, "ip": ip % P, "jq": jq % Q,
+                              "rrank": g.rrank, "crank": g.crank})
+    json.dump(grids, open(os.path.join(HERE, "grid.json"), "w"))
+    print("wrote zone_trace.json (%d cases), grid.json (%d grids)" % (len(cases), len(grids)))
+
+
+if __name__ == "__main__":
+    main()
