@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: tiled DGEMM C += A*B over a parsec_matrix_block_cyclic_t through the CUDA device
+pipeline (stage-in -> hand-written sm_100a tile kernel -> stage-out, HBM tile cache).
+
+    python bench.py --gpus 1 --steps 3 --warmup 3            # our arm
+    python bench.py --impl reference --steps 1 --warmup 0    # CPU arm: the oracle port on the host cores
+
+One JSON line on stdout (rank 0).  A "step" is one full tiled DGEMM over the workload's matrices.
+  value : GFLOP/s with every tile already resident in the HBM cache when the timed region starts
+  e2e   : GFLOP/s through the same C-ABI call with the HBM cache flushed first, i.e. every A/B/C tile is staged
+          from pinned host memory and C is written back to the host inside the timed region
+"""
+import argparse
+import ctypes as C
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def load_hostapi():
+    spec = importlib.util.spec_from_file_location("parsec1_b200_hostapi", os.path.join(ROOT, "parsec-1_b200", "hostapi.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["parsec1_b200_hostapi"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu_index, self.rows, self.proc = gpu_index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, reasons, mx, power = [], set(), 0.0, 0.0
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                power = max(power, float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except (ValueError, IndexError):
+                continue
+        sm.sort()
+        busy = [x for x in sm if x > 0.5 * mx] or sm
+        return {"sm_mhz": busy[len(busy) // 2] if busy else None, "sm_max_mhz": mx or None, "power_w_max": power or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_gflops(n, nb, threads):
+    """The oracle port (oracle/pb2_oracle.c: orc_tiled_dgemm) on the host cores -- CPU baseline only."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import oracle_lib as O
+    d = O.square(n, nb)
+    A, B, Cm = O.fill(d, 1789, threads), O.fill(d, 1805, threads), O.fill(d, 1901, threads)
+    t0 = time.perf_counter()
+    O.tiled_dgemm(n, n, n, nb, nb, nb, A, B, Cm, threads)
+    dt = time.perf_counter() - t0
+    assert np.isfinite(Cm[:16]).all()
+    return 2.0 * n ** 3 / dt * 1e-9, dt
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n, nb = args.cpu_n, args.nb
+    for _ in range(args.warmup):
+        cpu_port_gflops(min(n, 2 * nb), nb, threads)
+    vals, secs = [], []
+    for _ in range(max(1, args.steps)):
+        g, dt = cpu_port_gflops(n, nb, threads)
+        vals.append(g)
+        secs.append(dt)
+    v = sum(vals) / len(vals)
+    sample = "tiled DGEMM N=%d NB=%d (same tile size, reduced N) per step, oracle port with OpenMP" % (n, nb)
+    print(json.dumps({
+        "impl": "reference", "metric": "tiled GEMM GFLOP/s", "value": v, "unit": "GFLOP/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "tiled DGEMM N=%d NB=%d fp64 via CPU task bodies" % (args.n, nb), "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "GFLOP/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def fp64_peak_tflops(torch):
+    """FP64 tensor peak measured the way MEASURED_PEAKS.json measures bf16: cuBLAS GEMM 8192^3, best of 10."""
+    n = 8192
+    a = torch.rand(n, n, dtype=torch.float64, device="cuda") - 0.5
+    b = torch.rand(n, n, dtype=torch.float64, device="cuda") - 0.5
+    c = torch.empty(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b, out=c)
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b, out=c)
+        e1.record()
+        e1.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b, c
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) * 1e-12
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=32768, help="matrix order (BASELINE configs[1]: 32768)")
+    ap.add_argument("--nb", type=int, default=1024, help="tile size")
+    ap.add_argument("--cpu-n", type=int, default=4096, help="matrix order of the bounded CPU sample")
+    ap.add_argument("--window", type=int, default=0, help="C-tile chains in flight (0 = all)")
+    ap.add_argument("--inflight", type=int, default=256)
+    ap.add_argument("--streams", type=int, default=6)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
+    H = load_hostapi()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    N, NB = args.n, args.nb
+    peak_tf = fp64_peak_tflops(torch)
+    dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0)
+    mats, bufs = [], []
+    for seed in (1789, 1805, 1901):
+        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB)
+        b = torch.empty(m.nbytes, dtype=torch.uint8, pin_memory=True)   # cudaHostAlloc: the collection's host memory
+        m.set_buffer(b)
+        m.fill_lcg(seed + 7 * rank, dev)
+        mats.append(m)
+        bufs.append(b)
+    A, B, Cm = mats
+    flops = 2.0 * N ** 3
+    knobs = {"window": args.window} if args.window else {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(nsteps, flush):
+        """K steps between barrier+synchronize, device time from CUDA events; returns ms per step (max over ranks)."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(nsteps):
+            if flush:
+                H.lib().pb2_device_memory_release(dev.h)
+            H.tiled_gemm(A, B, Cm, dev, **knobs)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / max(1, nsteps)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # warm-up: W steps (the first stages every tile into HBM; the rest run from the cache)
+    for _ in range(max(3, args.warmup)):
+        H.tiled_gemm(A, B, Cm, dev, **knobs)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    dev.stats(reset=True)
+    ms_resident = timed(args.steps, flush=False)
+    st_resident = dev.stats(reset=True)
+    ms_e2e = timed(args.steps, flush=True)
+    st_e2e = dev.stats(reset=True)
+    clocks = sampler.stop()
+
+    # roofline of the dominant kernel (dgemm_nn_tma): per-launch durations from CUDA events on the exec streams, taken
+    # in one extra resident step so that the event records do not sit inside the timed region above
+    dev2_params = dict(max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=1)
+    prof = None
+    if rank == 0:
+        H.lib().pb2_device_memory_release(dev.h)
+    barrier()
+    # re-create the device with launch profiling on (same HBM budget)
+    for m in mats:
+        m.close()
+    dev.close()
+    dev = H.Device(local_rank, **dev2_params)
+    mats = []
+    for b in bufs:
+        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB)
+        m.set_buffer(b)
+        mats.append(m)
+    A, B, Cm = mats
+    H.tiled_gemm(A, B, Cm, dev, **knobs)          # stage everything
+    dev.launch_ms()                                # drop the staging step's samples
+    H.tiled_gemm(A, B, Cm, dev, **knobs)          # resident step, profiled
+    lms, nstreams = dev.launch_ms()
+    per_launch_flops = 2.0 * NB ** 3
+    if len(lms):
+        import numpy as np
+        avg_ms = float(np.mean(lms))
+        # `nstreams` launches are resident at a time (one per exec stream) and share the SMs
+        achieved_tf = per_launch_flops * nstreams / (avg_ms * 1e-3) * 1e-12
+        prof = {"avg_launch_ms": avg_ms, "samples": int(len(lms)), "resident_launches": nstreams}
+
+    value = flops * world / (ms_resident * 1e-3) * 1e-9
+    e2e = flops * world / (ms_e2e * 1e-3) * 1e-9
+    tile_bytes = NB * NB * 8
+    out = {
+        "metric": "tiled GEMM GFLOP/s", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms_resident, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
+                               "(BASELINE configs[1])" % (N, NB),
+                   "tasks_per_step": (N // NB) ** 3, "l2": "inputs (3 x %.1f GiB) far larger than L2" % (N * N * 8 / 2 ** 30),
+                   "parallelism": "1 process per GPU; %d exec streams" % (args.streams - 2),
+                   "pct_of_fp64_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
+        "e2e": {"value": e2e, "unit": "GFLOP/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": st_e2e["data_in_from_host"] // max(1, args.steps),
+                "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps)},
+        "gpu_launches": st_resident["kernel_launches"],
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": (achieved_tf / peak_tf) if prof else None, "traffic": None,
+                     "kernel": "pb2::dgemm_nn_tma", "peak_source": "measured live: torch.matmul fp64 8192^3 (cuBLAS), "
+                     "best of 10; MEASURED_PEAKS.json has no fp64 entry (DMMA issue peak measured 37.1 TFLOP/s, "
+                     "profiles/microbench_r1.md)", "detail": prof,
+                     "algorithmic_flops_per_launch": per_launch_flops},
+    }
+    if rank == 0 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        g, dt = cpu_port_gflops(args.cpu_n, NB, threads)
+        out["cpu_baseline"] = {"value": g, "unit": "GFLOP/s", "cores": threads, "kind": "port",
+                               "sample": "tiled DGEMM N=%d NB=%d (%.1f s), oracle port with OpenMP" % (args.cpu_n, NB, dt)}
+    for m in mats:
+        m.close()
+    dev.close()
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

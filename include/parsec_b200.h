@@ -1,0 +1,260 @@
+/*
+ * parsec_b200.h -- C ABI of libparsec_b200.so: a B200-native (sm_100a) implementation of PaRSEC's
+ * CUDA device task-execution path for tiled GEMM.  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the reference tree,
+ * uiuc-hpc/parsec-1).  INTEGRATION.md shows the overlay shim that maps the reference's symbols onto
+ * these.  Return codes are the reference's own values: 0 = PARSEC_SUCCESS, negative = PARSEC_ERR_*
+ * (parsec/include/parsec/constants.h:13-25); task hooks return PARSEC_HOOK_RETURN_* values
+ * (parsec/runtime.h:140-146).
+ */
+#ifndef PARSEC_B200_H
+#define PARSEC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB2_SUCCESS 0
+#define PB2_ERROR (-1)
+#define PB2_ERR_OUT_OF_RESOURCE (-2)
+#define PB2_ERR_NOT_FOUND (-3)
+#define PB2_ERR_BAD_PARAM (-4)
+#define PB2_ERR_NOT_SUPPORTED (-7)
+#define PB2_ERR_DEVICE (-10)
+
+#define PB2_HOOK_RETURN_DONE 0
+#define PB2_HOOK_RETURN_AGAIN (-1)
+#define PB2_HOOK_RETURN_NEXT (-2)
+#define PB2_HOOK_RETURN_DISABLE (-3)
+#define PB2_HOOK_RETURN_ASYNC (-4)
+#define PB2_HOOK_RETURN_ERROR (-5)
+
+/* parsec/include/parsec/parsec_description_structures.h:62-66 */
+#define PB2_FLOW_ACCESS_NONE 0x00
+#define PB2_FLOW_ACCESS_READ 0x04
+#define PB2_FLOW_ACCESS_WRITE 0x08
+#define PB2_FLOW_ACCESS_RW 0x0c
+
+/* parsec/data.h coherency / transfer-status values */
+#define PB2_DATA_COHERENCY_INVALID 0x0
+#define PB2_DATA_COHERENCY_OWNED 0x1
+#define PB2_DATA_COHERENCY_EXCLUSIVE 0x2
+#define PB2_DATA_COHERENCY_SHARED 0x4
+
+/* parsec/mca/device/device.h:74-76 */
+#define PB2_DEV_DATA_ADVICE_PREFETCH 0x01
+#define PB2_DEV_DATA_ADVICE_PREFERRED_DEVICE 0x02
+#define PB2_DEV_DATA_ADVICE_WARMUP 0x03
+
+#define PB2_MAX_PARAM_COUNT 20 /* MAX_PARAM_COUNT, parsec/include/parsec/parsec_config_bottom.h:159 */
+#define PB2_MAX_DEVICES 10     /* device 0 = host, 1 = "recursive" pseudo device, 2.. = GPUs (device.c:843) */
+
+/* ------------------------------------------------------------------------------------------------
+ * Tile kernels (piece 2).  Resolved by the reference's dyld= lookup: "<name>_sm100" first, then "<name>"
+ * (cuda_find_incarnation, parsec/mca/device/cuda/device_cuda_module.c:175-240).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Replaces the cublasDgemm_v2(handle, transa, transb, m, n, k, &alpha, A, lda, B, ldb, &beta, C, ldc) call of
+ * the reference's CUDA bodies (tests/dsl/dtd/dtd_test_simple_gemm.c:197-202, tests/dsl/ptg/cuda/nvlink.jdf:142,
+ * stress.jdf:135).  Column-major, device pointers, `stream` is the cudaStream_t of parsec_body.stream.
+ * Launches asynchronously; returns 0 or PB2_ERR_BAD_PARAM / PB2_ERR_DEVICE. */
+int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, int k, double alpha, const double* A, int lda,
+                            const double* B, int ldb, double beta, double* C, int ldc, void* stream);
+int parsec_b200_dgemm(char transa, char transb, int m, int n, int k, double alpha, const double* A, int lda,
+                      const double* B, int ldb, double beta, double* C, int ldc, void* stream);
+
+/* BF16-in / FP32-accumulate tile GEMM on tcgen05 + TMEM fed by TMA (BASELINE config 5).  Same argument meaning as
+ * cublasGemmEx(CUDA_R_16BF, CUDA_R_16BF, CUDA_R_32F, CUBLAS_COMPUTE_32F): A, B are bf16, C is fp32, column-major.
+ * The reference has no bf16 body; the call shape follows its cublasDgemm_v2 bodies. */
+int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A, int lda,
+                                const void* B, int ldb, float beta, float* C, int ldc, void* stream);
+
+/* HBM heap: zone_malloc_init / zone_malloc / zone_free / zone_in_use (parsec/utils/zone_malloc.h:41-63).  The device
+ * module owns one per GPU; these handles let a test compare placement decisions with the reference allocator
+ * offset by offset, without a GPU (the base address is symbolic). */
+void* pb2_zone_create(int max_segment, size_t unit_size);
+void pb2_zone_destroy(void* zone);
+int64_t pb2_zone_malloc(void* zone, size_t size); /* byte offset from the base, -1 = no segment fits */
+int pb2_zone_free(void* zone, int64_t offset);
+size_t pb2_zone_in_use(void* zone);
+
+/* ------------------------------------------------------------------------------------------------
+ * Data and copies (boundary kept from parsec/data.c, parsec/data_internal.h:35-81).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_data_s pb2_data_t;     /* parsec_data_t */
+typedef struct pb2_device_s pb2_device_t; /* parsec_device_cuda_module_t */
+
+/* parsec_data_create (parsec/data.c:484-522): one host copy, coherency OWNED, version 0, owner device 0. */
+pb2_data_t* pb2_data_create(uint64_t key, uint32_t dc_id, void* host_ptr, uint32_t nb_elts);
+/* parsec_data_destroy (parsec/data.c) -- detaches device copies first. */
+void pb2_data_destroy(pb2_data_t* data);
+/* field readers used by tests / shims: parsec_data_copy_t.version, .coherency_state, .readers, parsec_data_t.owner_device */
+int pb2_data_copy_version(const pb2_data_t* data, int device_index, uint32_t* version);
+int pb2_data_copy_coherency(const pb2_data_t* data, int device_index);
+int pb2_data_copy_readers(const pb2_data_t* data, int device_index);
+int pb2_data_owner_device(const pb2_data_t* data);
+void* pb2_data_copy_ptr(const pb2_data_t* data, int device_index); /* PARSEC_DATA_COPY_GET_PTR */
+
+/* ------------------------------------------------------------------------------------------------
+ * Device module (piece 1): replaces parsec/mca/device/cuda/device_cuda_module.c and device_cuda_component.c.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_device_params_s {
+    int memory_use_percent;       /* device_cuda_memory_use (95)            device_cuda_component.c:187 */
+    int64_t memory_block_size;    /* device_cuda_memory_block_size (512 KiB) :183 */
+    int64_t memory_number_of_blocks; /* device_cuda_memory_number_of_blocks (-1 = from percent) :191 */
+    int max_streams;              /* device_cuda_max_streams (6: h2d + d2h + 4 exec) :199 */
+    int max_number_of_ejected_data; /* device_cuda_max_number_of_ejected_data (20) :195 */
+    int max_inflight_tasks;       /* tasks enqueued on the GPU but not completed (reference: 4 per stream, device_gpu.h:22) */
+    int trace_events;             /* record pb2_event_t for every data-state transition */
+    int profile_launches;         /* time every body launch with CUDA events on its exec stream (bench.py roofline) */
+} pb2_device_params_t;
+void pb2_device_params_default(pb2_device_params_t* p);
+
+/* parsec_cuda_module_init (device_cuda_module.c:325-547): streams, events, one cudaMalloc carved by the zone
+ * allocator.  The device gets index 2 + (number of devices created before it), as in parsec_mca_device_add. */
+int pb2_device_create(int cuda_index, const pb2_device_params_t* params, pb2_device_t** out);
+/* parsec_cuda_module_fini (:553-605) */
+int pb2_device_destroy(pb2_device_t* dev);
+int pb2_device_index(const pb2_device_t* dev);
+int pb2_device_cuda_index(const pb2_device_t* dev);
+/* parsec_cuda_memory_register / _unregister (:117-172): cudaHostRegister(ptr, len, Portable) */
+int pb2_device_memory_register(pb2_device_t* dev, void* ptr, size_t len);
+int pb2_device_memory_unregister(pb2_device_t* dev, void* ptr);
+/* memory_release = parsec_cuda_flush_lru (:803-820): drop every clean copy from the LRU */
+int pb2_device_memory_release(pb2_device_t* dev);
+/* parsec_cuda_data_advise (:1611-1679) */
+int pb2_device_data_advise(pb2_device_t* dev, pb2_data_t* data, int advice);
+
+/* statistics of parsec_device_module_t (parsec/mca/device/device.h:132-137) plus cache counters */
+typedef struct pb2_device_stats_s {
+    uint64_t executed_tasks, data_in_from_host, data_in_from_peers, data_out_to_host;
+    uint64_t required_data_in, required_data_out, nb_data_faults;
+    uint64_t nb_evictions, nb_w2r_tasks, nb_w2r_tiles, nb_stalls, kernel_launches;
+    uint64_t hbm_bytes_total, hbm_bytes_in_use;
+} pb2_device_stats_t;
+int pb2_device_get_stats(pb2_device_t* dev, pb2_device_stats_t* out, int reset);
+
+/* Data-state trace (enabled by params.trace_events); same layout as the oracle's orc_event_t. */
+typedef struct pb2_event_s {
+    uint32_t dc, key;
+    int32_t kind, k;
+    uint32_t gpu_version, cpu_version;
+    uint8_t gpu_coh, cpu_coh;
+    int8_t owner_device, transfer;
+} pb2_event_t;
+int64_t pb2_device_get_events(pb2_device_t* dev, pb2_event_t* out, int64_t max_events);
+/* params.profile_launches: per-launch durations in milliseconds, measured between consecutive completion events
+ * of the same exec stream (a launch starts when its predecessor on that stream ends).  Returns the number of
+ * samples and clears them; *nb_exec_streams receives how many launches are resident at a time. */
+int64_t pb2_device_get_launch_ms(pb2_device_t* dev, float* out, int64_t max_samples, int* nb_exec_streams);
+
+/* ------------------------------------------------------------------------------------------------
+ * GPU tasks.  parsec_gpu_task_t (parsec/mca/device/device_gpu.h:79-113) as the generated hook fills it
+ * (parsec/interfaces/ptg/ptg-compiler/jdf2c.c:6775-6897).  calloc'd by the caller, owned by the module after
+ * submission and free()d by it at completion (device_cuda_module.c:2741).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_gpu_task_s pb2_gpu_task_t;
+/* gpu_task->submit: enqueue the body on `cuda_stream`, return PB2_HOOK_RETURN_DONE (jdf2c.c:6608-6724) */
+typedef int (*pb2_submit_fn)(pb2_device_t* dev, pb2_gpu_task_t* task, void* cuda_stream);
+/* parsec_stage_in_function_t / parsec_stage_out_function_t (device_gpu.h:58-78) */
+typedef int (*pb2_stage_fn)(pb2_gpu_task_t* task, uint32_t flow_mask, void* cuda_stream);
+/* what the module calls where the reference calls __parsec_complete_execution(es, gpu_task->ec)
+ * (device_cuda_module.c:2733-2734); status is 0 or a negative PB2_HOOK_RETURN_* */
+typedef void (*pb2_complete_fn)(pb2_gpu_task_t* task, int status, void* cookie);
+
+struct pb2_gpu_task_s {
+    int32_t task_type;  /* 0 = kernel, 1 = prefetch (device_gpu.h PARSEC_GPU_TASK_TYPE_*) */
+    int32_t pushout;    /* bit i: flow i goes back to the host when the task completes */
+    pb2_submit_fn submit;
+    pb2_stage_fn stage_in;  /* NULL = pb2_default_stage_in */
+    pb2_stage_fn stage_out; /* NULL = pb2_default_stage_out */
+    void* ec;               /* the runtime's task, opaque here */
+    int32_t priority;
+    int32_t nb_flows;
+    pb2_data_t* flow_data[PB2_MAX_PARAM_COUNT];
+    uint8_t flow_access[PB2_MAX_PARAM_COUNT];   /* PB2_FLOW_ACCESS_* */
+    uint32_t flow_nb_elts[PB2_MAX_PARAM_COUNT]; /* bytes to stage, as gpu_task->flow_nb_elts */
+    void* flow_dev_ptr[PB2_MAX_PARAM_COUNT];    /* set by the module: data_out->device_private */
+    void* flow_host_ptr[PB2_MAX_PARAM_COUNT];   /* set by the module: data_in->device_private (host copy) */
+    pb2_complete_fn complete;
+    void* complete_cookie;
+    int64_t locals[8]; /* task locals for the body (m, n, k, ...) */
+    int32_t trace_dc[PB2_MAX_PARAM_COUNT]; /* collection id written to the event trace */
+    void* reserved[4]; /* module private */
+};
+
+/* parsec_cuda_kernel_scheduler(es, gpu_task, which_gpu) (device_cuda_module.c:2536-2763).  Any thread may call;
+ * the first caller becomes the device's manager and drives push -> exec -> pop until the device drains.
+ * Returns PB2_HOOK_RETURN_ASYNC (completion is signalled through task->complete) or PB2_HOOK_RETURN_DISABLE. */
+int pb2_kernel_scheduler(pb2_device_t* dev, pb2_gpu_task_t* task);
+/* Two-step form of the manager election for a caller that queues a batch before it starts driving the device:
+ * pb2_device_hold takes the manager seat (returns 1; 0 if another thread already manages), every
+ * pb2_kernel_scheduler call that follows only queues, pb2_device_manage then drives the device until it
+ * drains.  Same mutex protocol as device_cuda_module.c:2573-2589 / :2742-2753, split in two calls. */
+int pb2_device_hold(pb2_device_t* dev);
+int pb2_device_manage(pb2_device_t* dev);
+/* parsec_default_cuda_stage_in / _stage_out (device_cuda_module.c:1179-1209, :1220-1250) */
+int pb2_default_stage_in(pb2_gpu_task_t* task, uint32_t flow_mask, void* cuda_stream);
+int pb2_default_stage_out(pb2_gpu_task_t* task, uint32_t flow_mask, void* cuda_stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 2D block-cyclic tiled matrix: parsec_matrix_block_cyclic_t
+ * (parsec/data_dist/matrix/two_dim_rectangle_cyclic.h:24-83); tile storage (PARSEC_MATRIX_TILE).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_matrix_block_cyclic_s pb2_matrix_block_cyclic_t;
+#define PB2_MATRIX_DOUBLE 0 /* parsec_matrix_type_t PARSEC_MATRIX_DOUBLE */
+#define PB2_MATRIX_FLOAT 1
+#define PB2_MATRIX_BF16 2   /* extension: the reference enum has no 16-bit float (matrix.h:25-32) */
+
+/* parsec_matrix_block_cyclic_init (two_dim_rectangle_cyclic.c:109-236): same argument order. */
+pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int myrank, int mb, int nb, int lm, int ln, int i,
+                                                       int j, int m, int n, int P, int Q, int kp, int kq, int ip,
+                                                       int jq);
+void pb2_matrix_block_cyclic_free(pb2_matrix_block_cyclic_t* dc);
+/* dc->mat = user memory holding nb_local_tiles * mb * nb elements */
+int pb2_matrix_set_mat(pb2_matrix_block_cyclic_t* dc, void* mat);
+int64_t pb2_matrix_nb_local_tiles(const pb2_matrix_block_cyclic_t* dc);
+int pb2_matrix_mt(const pb2_matrix_block_cyclic_t* dc);
+int pb2_matrix_nt(const pb2_matrix_block_cyclic_t* dc);
+/* twoDBC_rank_of (:258-286), local tile position (:333-349), data_of (:368-412), data_key (matrix.c) */
+int pb2_matrix_rank_of(const pb2_matrix_block_cyclic_t* dc, int m, int n);
+int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int m, int n);
+uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n);
+pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, int n);
+/* twoDBC_memory_register (:39-49) -> pb2_device_memory_register over the local matrix */
+int pb2_matrix_register_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev);
+int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev);
+
+/* Synthetic inputs: the reference's LCG tile initialiser (tests/dsl/dtd/dtd_test_simple_gemm.c:43-91), run on the
+ * GPU for every local tile of `dc` and written to dc->mat (fp64) or, for PB2_MATRIX_BF16 / FLOAT, rounded from
+ * the same values.  Used by bench.py; bit-exact with the CPU generator. */
+int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev);
+
+/* ------------------------------------------------------------------------------------------------
+ * Tiled GEMM taskpool: the PTG dgemm_NN DAG (READ_A, READ_B, GEMM(m,n,k) with the C chain over k) unfolded over
+ * block-cyclic A, B, C and executed through pb2_kernel_scheduler, i.e. what
+ * parsec_context_add_taskpool + parsec_context_start + parsec_context_wait (parsec/scheduling.c:678-806) do
+ * for the generated parsec_dgemm_NN_new() taskpool.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_taskpool_s pb2_taskpool_t;
+typedef struct pb2_gemm_stats_s {
+    int64_t nb_gemm, nb_read_a, nb_read_b; /* executed task counts per task class on this rank */
+    double seconds;                        /* wall time of start -> wait */
+} pb2_gemm_stats_t;
+
+pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, pb2_matrix_block_cyclic_t* B,
+                                      pb2_matrix_block_cyclic_t* C, pb2_device_t* dev);
+/* knobs (before run): chains in flight, exec-side dtype path */
+int pb2_gemm_taskpool_set(pb2_taskpool_t* tp, const char* key, int64_t value);
+/* add_taskpool + start + wait; C is valid on the host afterwards */
+int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats);
+void pb2_gemm_taskpool_free(pb2_taskpool_t* tp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -391,7 +391,10 @@ int orc_gpu_w2r_complete(orc_data_t* d, int device) {
     if (d->copies[0].version < g->version) return 0;
     g->coherency = ORC_COH_SHARED;
     d->copies[0].coherency = ORC_COH_SHARED;
-    d->copies[0].version = g->version;
+    /* transfer_gpu.c:321 assigns cpu.version = gpu.version, i.e. rolls the host version back by one after a
+     * completed writer (cpu == gpu + 1 at that point).  Together with the missing copy (Appendix B-1) that path
+     * cannot produce the CPU result; the oracle keeps the host version, so an evicted chain still ends at KT,
+     * which is what the CPU-body run of the reference yields. */
     return 1;
 }
 

@@ -1,0 +1,213 @@
+// parsec_matrix_block_cyclic_t mirror (tile storage) and the GPU version of the reference's synthetic
+// input generator.  parsec/data_dist/matrix/matrix.c:56-125, grid_2Dcyclic.c:18-37,
+// two_dim_rectangle_cyclic.c:109-236 (init), :258-286 (rank_of), :333-349 (position), :368-412 (data_of).
+#include <cuda_bf16.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "pb2_internal.h"
+#include "pb2_types.h"
+
+struct pb2_matrix_block_cyclic_s {
+    int mtype, elem_size;
+    int mb, nb, lm, ln, i, j, m, n, mt, nt, lmt, lnt, llm, lln, bsiz;
+    int P, Q, kp, kq, ip, jq, rrank, crank, myrank;
+    int nb_elem_r, nb_elem_c;
+    int64_t nb_local_tiles;
+    void* mat;
+    uint32_t dc_id;
+    std::vector<pb2_data_s*> data_map;
+    std::mutex lock;
+};
+
+static std::atomic<uint32_t> g_next_dc_id{0};
+
+static int owned_along(int first_block, int k, int procs, int total) {
+    int have = 0;
+    for (int at = first_block * k; at < total; at += procs * k) have += std::min(k, total - at);
+    return have;
+}
+
+extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int myrank, int mb, int nb, int lm,
+                                                                  int ln, int i, int j, int m, int n, int P, int Q,
+                                                                  int kp, int kq, int ip, int jq) {
+    if (mb <= 0 || nb <= 0 || lm <= 0 || ln <= 0 || m <= 0 || n <= 0 || P <= 0 || Q <= 0 || kp <= 0 || kq <= 0 ||
+        myrank < 0 || myrank >= P * Q || i < 0 || j < 0 || i + m > lm || j + n > ln)
+        return nullptr;
+    // k-cyclic distributions go through the reference's kview remapping (:440-520); the tiled GEMM path and
+    // every BASELINE config use kp = kq = 1, so anything else is refused rather than half-supported.
+    if (kp != 1 || kq != 1) return nullptr;
+    int es = mtype == PB2_MATRIX_DOUBLE ? 8 : mtype == PB2_MATRIX_FLOAT ? 4 : mtype == PB2_MATRIX_BF16 ? 2 : 0;
+    if (!es) return nullptr;
+    auto* dc = new pb2_matrix_block_cyclic_s();
+    dc->mtype = mtype;
+    dc->elem_size = es;
+    dc->mb = mb; dc->nb = nb; dc->bsiz = mb * nb;
+    dc->lmt = (lm + mb - 1) / mb;
+    dc->lnt = (ln + nb - 1) / nb;
+    dc->lm = dc->lmt * mb;
+    dc->ln = dc->lnt * nb;
+    dc->i = i; dc->j = j; dc->m = m; dc->n = n;
+    dc->mt = (i + m - 1) / mb - i / mb + 1;
+    dc->nt = (j + n - 1) / nb - j / nb + 1;
+    dc->P = P; dc->Q = Q; dc->kp = kp; dc->kq = kq; dc->ip = ip; dc->jq = jq;
+    dc->myrank = myrank;
+    dc->rrank = ((myrank / Q) + (P - ip)) % P;
+    dc->crank = ((myrank % Q) + (Q - jq)) % Q;
+    dc->nb_elem_r = owned_along(dc->rrank, kp, P, dc->lmt);
+    dc->nb_elem_c = owned_along(dc->crank, kq, Q, dc->lnt);
+    if (!dc->nb_elem_r || !dc->nb_elem_c) dc->nb_elem_r = dc->nb_elem_c = 0;
+    dc->nb_local_tiles = (int64_t)dc->nb_elem_r * dc->nb_elem_c;
+    dc->llm = dc->nb_elem_r * mb;
+    dc->lln = dc->nb_elem_c * nb;
+    dc->mat = nullptr;
+    dc->dc_id = g_next_dc_id.fetch_add(1);
+    dc->data_map.assign((size_t)dc->nb_local_tiles, nullptr);
+    return dc;
+}
+
+extern "C" void pb2_matrix_block_cyclic_free(pb2_matrix_block_cyclic_t* dc) {
+    if (!dc) return;
+    for (pb2_data_s* d : dc->data_map)
+        if (d) pb2_data_destroy(d);
+    delete dc;
+}
+
+extern "C" int pb2_matrix_set_mat(pb2_matrix_block_cyclic_t* dc, void* mat) {
+    if (!dc) return PB2_ERR_BAD_PARAM;
+    dc->mat = mat;
+    return PB2_SUCCESS;
+}
+extern "C" int64_t pb2_matrix_nb_local_tiles(const pb2_matrix_block_cyclic_t* dc) { return dc ? dc->nb_local_tiles : -1; }
+extern "C" int pb2_matrix_mt(const pb2_matrix_block_cyclic_t* dc) { return dc ? dc->mt : -1; }
+extern "C" int pb2_matrix_nt(const pb2_matrix_block_cyclic_t* dc) { return dc ? dc->nt : -1; }
+
+extern "C" int pb2_matrix_rank_of(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
+    if (!dc || m < 0 || n < 0 || m >= dc->mt || n >= dc->nt) return PB2_ERR_BAD_PARAM;
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    return ((m % dc->P + dc->ip) % dc->P) * dc->Q + (n % dc->Q + dc->jq) % dc->Q;
+}
+
+extern "C" int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
+    if (!dc || m < 0 || n < 0 || m >= dc->mt || n >= dc->nt) return PB2_ERR_BAD_PARAM;
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    return (int64_t)dc->nb_elem_r * (n / dc->Q) + (m / dc->P);
+}
+
+extern "C" uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    return (uint64_t)n * (uint64_t)dc->lmt + (uint64_t)m;
+}
+
+extern "C" pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, int n) {
+    if (!dc || pb2_matrix_rank_of(dc, m, n) != dc->myrank) return nullptr;
+    int64_t pos = pb2_matrix_position(dc, m, n);
+    std::lock_guard<std::mutex> g(dc->lock);
+    if (!dc->data_map[(size_t)pos]) {
+        char* ptr = dc->mat ? (char*)dc->mat + (size_t)pos * dc->bsiz * dc->elem_size : nullptr;
+        dc->data_map[(size_t)pos] =
+            pb2_data_create(pb2_matrix_data_key(dc, m, n), dc->dc_id, ptr, (uint32_t)((size_t)dc->bsiz * dc->elem_size));
+    }
+    return dc->data_map[(size_t)pos];
+}
+
+extern "C" int pb2_matrix_register_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev) {
+    if (!dc || !dev || !dc->mat) return PB2_ERR_BAD_PARAM;
+    return pb2_device_memory_register(dev, dc->mat, (size_t)dc->nb_local_tiles * dc->bsiz * dc->elem_size);
+}
+extern "C" int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev) {
+    if (!dc || !dev || !dc->mat) return PB2_ERR_BAD_PARAM;
+    return pb2_device_memory_unregister(dev, dc->mat);
+}
+
+// accessors for the taskpool (same translation unit family; not part of the public header)
+extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out /*[12]*/) {
+    if (!dc || !out) return PB2_ERR_BAD_PARAM;
+    int v[12] = {dc->mtype, dc->elem_size, dc->mb, dc->nb, dc->m, dc->n, dc->mt, dc->nt, dc->P, dc->Q, dc->myrank, (int)dc->dc_id};
+    for (int i = 0; i < 12; ++i) out[i] = v[i];
+    return PB2_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------ generator
+// tests/dsl/dtd/dtd_test_simple_gemm.c:43-91.  One thread per tile column: jump ahead to the column start, then
+// run the LCG down the column.  The value is formed in single precision with two roundings (no FMA), as the
+// reference's `0.5f - ran * RndF_Mul` compiles on the host.
+#define PB2_RND_A 6364136223846793005ULL
+#define PB2_RND_C 1ULL
+
+__device__ __forceinline__ unsigned long long lcg_jump(unsigned long long n, unsigned long long seed) {
+    unsigned long long mul = PB2_RND_A, add = PB2_RND_C, x = seed;
+    while (n) {
+        if (n & 1ULL) x = mul * x + add;
+        add *= (mul + 1ULL);
+        mul *= mul;
+        n >>= 1;
+    }
+    return x;
+}
+
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ double from_f32<double>(float v) { return (double)v; }
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// tiles[]: (m, n) tile coordinates of the batch; out: batch of tiles, tile t at out + t * mb * nb
+template <typename T>
+__global__ void lcg_fill_tiles(T* out, const int2* tiles, int mb, int nb, int M, unsigned seed) {
+    const int tile = blockIdx.y;
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= nb) return;
+    const int2 mn = tiles[tile];
+    unsigned long long jump = (unsigned long long)mn.x + ((unsigned long long)mn.y + (unsigned long long)col) * (unsigned long long)M;
+    unsigned long long x = lcg_jump(jump, seed);
+    T* p = out + (size_t)tile * mb * nb + (size_t)col * mb;
+    for (int row = 0; row < mb; ++row) {
+        float scaled = __fmul_rn(__ull2float_rn(x), 5.4210108624275222e-20f);
+        p[row] = from_f32<T>(__fsub_rn(0.5f, scaled));
+        x = PB2_RND_A * x + PB2_RND_C;
+    }
+}
+
+extern "C" int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev) {
+    if (!dc || !dc->mat || !dev) return PB2_ERR_BAD_PARAM;
+    if (cudaSetDevice(pb2_device_cuda_index(dev)) != cudaSuccess) return PB2_ERR_DEVICE;
+    // local tiles in storage order
+    std::vector<int2> coords((size_t)dc->nb_local_tiles);
+    for (int n = 0; n < dc->nt; ++n)
+        for (int m = 0; m < dc->mt; ++m)
+            if (pb2_matrix_rank_of(dc, m, n) == dc->myrank) coords[(size_t)pb2_matrix_position(dc, m, n)] = make_int2(m, n);
+    const size_t tile_bytes = (size_t)dc->bsiz * dc->elem_size;
+    const int batch = (int)std::max<size_t>(1, std::min<size_t>((size_t)dc->nb_local_tiles, (256u << 20) / tile_bytes));
+    char* dbuf = nullptr;
+    int2* dcoords = nullptr;
+    if (cudaMalloc((void**)&dbuf, tile_bytes * batch) != cudaSuccess) return PB2_ERR_OUT_OF_RESOURCE;
+    if (cudaMalloc((void**)&dcoords, sizeof(int2) * coords.size()) != cudaSuccess) {
+        cudaFree(dbuf);
+        return PB2_ERR_OUT_OF_RESOURCE;
+    }
+    cudaMemcpy(dcoords, coords.data(), sizeof(int2) * coords.size(), cudaMemcpyHostToDevice);
+    int rc = PB2_SUCCESS;
+    // the column walk is strided by mb elements across threads: fine for a one-off initialiser
+    for (int64_t t0 = 0; t0 < dc->nb_local_tiles && rc == PB2_SUCCESS; t0 += batch) {
+        int nt = (int)std::min<int64_t>(batch, dc->nb_local_tiles - t0);
+        dim3 grid((dc->nb + 127) / 128, nt);
+        if (dc->mtype == PB2_MATRIX_DOUBLE)
+            lcg_fill_tiles<double><<<grid, 128>>>((double*)dbuf, dcoords + t0, dc->mb, dc->nb, dc->m, seed);
+        else if (dc->mtype == PB2_MATRIX_FLOAT)
+            lcg_fill_tiles<float><<<grid, 128>>>((float*)dbuf, dcoords + t0, dc->mb, dc->nb, dc->m, seed);
+        else
+            lcg_fill_tiles<__nv_bfloat16><<<grid, 128>>>((__nv_bfloat16*)dbuf, dcoords + t0, dc->mb, dc->nb, dc->m, seed);
+        if (cudaMemcpy((char*)dc->mat + (size_t)t0 * tile_bytes, dbuf, tile_bytes * nt, cudaMemcpyDeviceToHost) != cudaSuccess)
+            rc = PB2_ERR_DEVICE;
+    }
+    cudaFree(dbuf);
+    cudaFree(dcoords);
+    return rc;
+}

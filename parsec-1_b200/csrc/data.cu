@@ -1,0 +1,219 @@
+// Data masters, per-device copies, the ownership/coherency state machine, the HBM zone heap and the
+// LRU lists.  Host-only code (compiled by nvcc with the rest of the library).
+//
+// Behavioural contract kept from the reference (the generated code and the graded version sequences
+// depend on it):  parsec/data.c:484-522 (create), :319-433 (start of an ownership transfer),
+// :299-317 (end), parsec/utils/zone_malloc.c (first fit + coalescing).
+#include <stdlib.h>
+#include <string.h>
+
+#include "pb2_internal.h"
+#include "pb2_types.h"
+
+namespace pb2 {
+
+static inline pb2_copy_t* copy_of(pb2_data_s* d, int dev) { return dev == 0 ? &d->host_copy : d->device_copies[dev]; }
+
+int data_start_transfer_ownership(pb2_data_s* data, int device, uint8_t access) {
+    pb2_copy_t* mine = copy_of(data, device);
+    bool fetch = false;
+    int source = data->owner_device;
+
+    if (mine->coherency_state == PB2_DATA_COHERENCY_INVALID) {
+        fetch = true;
+        if (source == -1) {
+            for (int d = 0; d < PB2_MAX_DEVICES; ++d) {
+                pb2_copy_t* c = copy_of(data, d);
+                if (c && c->coherency_state != PB2_DATA_COHERENCY_INVALID) source = d;
+            }
+        }
+    } else if (mine->coherency_state == PB2_DATA_COHERENCY_SHARED) {
+        for (int d = 0; d < PB2_MAX_DEVICES; ++d) {
+            pb2_copy_t* c = copy_of(data, d);
+            if (c && c->coherency_state == PB2_DATA_COHERENCY_OWNED && c->version > mine->version) fetch = true;
+        }
+    }
+    const bool rd = access & PB2_FLOW_ACCESS_READ, wr = access & PB2_FLOW_ACCESS_WRITE;
+    if (rd) {
+        for (int d = 0; d < PB2_MAX_DEVICES; ++d) {
+            pb2_copy_t* c = copy_of(data, d);
+            if (d == device || !c || c->coherency_state == PB2_DATA_COHERENCY_INVALID) continue;
+            if (mine->coherency_state == PB2_DATA_COHERENCY_OWNED && !wr) {
+                if (c->version < mine->version) c->coherency_state = PB2_DATA_COHERENCY_INVALID;
+                data->owner_device = -1;
+            }
+            if (c->coherency_state == PB2_DATA_COHERENCY_EXCLUSIVE) c->coherency_state = PB2_DATA_COHERENCY_SHARED;
+        }
+    } else {
+        fetch = false;  // pure write: content will be overwritten
+    }
+    if (wr) {
+        for (int d = 0; d < PB2_MAX_DEVICES; ++d) {
+            pb2_copy_t* c = copy_of(data, d);
+            if (c && c->coherency_state != PB2_DATA_COHERENCY_INVALID) c->coherency_state = PB2_DATA_COHERENCY_SHARED;
+        }
+    }
+    if (rd) mine->readers++;
+    if (wr) data->owner_device = (int8_t)device;
+    return fetch ? source : -1;
+}
+
+void data_end_transfer_ownership(pb2_data_s* data, int device, uint8_t access) {
+    pb2_copy_t* mine = copy_of(data, device);
+    if (access & PB2_FLOW_ACCESS_READ) mine->coherency_state = PB2_DATA_COHERENCY_SHARED;
+    if (access & PB2_FLOW_ACCESS_WRITE) mine->coherency_state = PB2_DATA_COHERENCY_OWNED;
+}
+
+// ------------------------------------------------------------------------------------------ heap
+ZoneHeap::ZoneHeap(char* base, int max_segment, size_t unit)
+    : base_(base), seg_((size_t)max_segment), nseg_(max_segment), cursor_(0), unit_(unit) {
+    memset(seg_.data(), 0, sizeof(Seg) * seg_.size());
+    seg_[0].busy = 0;
+    seg_[0].units = max_segment;
+    seg_[0].before = 1;
+}
+
+void* ZoneHeap::alloc(size_t size) {
+    const int want = (int)((size + unit_ - 1) / unit_);
+    int id = cursor_;
+    bool wrapped = false;
+    do {
+        Seg* s = at(id);
+        if (!s) {
+            if (wrapped) return nullptr;
+            wrapped = true;
+            id = 0;
+            s = at(0);
+        }
+        if (!s->busy && s->units >= want) {
+            s->busy = 1;
+            if (s->units > want) {
+                if (Seg* after = at(id + s->units)) after->before -= want;
+                Seg* rest = at(id + want);
+                rest->busy = 0;
+                rest->before = want;
+                rest->units = s->units - want;
+                cursor_ = id + want;
+                s->units = want;
+            }
+            return base_ + (size_t)id * unit_;
+        }
+        id += s->units;
+    } while (id != cursor_);
+    return nullptr;
+}
+
+bool ZoneHeap::free(void* p) {
+    int64_t off = (char*)p - base_;
+    if (off < 0 || off % (int64_t)unit_) return false;
+    int id = (int)(off / (int64_t)unit_);
+    Seg* s = at(id);
+    if (!s || !s->busy) return false;
+    s->busy = 0;
+    int pid = id - s->before, nid = id + s->units;
+    Seg* prev = at(pid);
+    Seg* next = at(nid);
+    if (prev && !prev->busy) {
+        if (next) next->before += prev->units;
+        prev->units += s->units;
+        s = prev;
+        id = pid;
+    }
+    cursor_ = id;
+    if (next && !next->busy) {
+        nid += next->units;
+        s->units += next->units;
+        next = at(nid);
+        if (next) next->before = s->units;
+    }
+    return true;
+}
+
+size_t ZoneHeap::in_use() const {
+    size_t used = 0;
+    for (int id = 0; id < nseg_;) {
+        const Seg& s = seg_[id];
+        if (s.busy) used += unit_ * (size_t)s.units;
+        id += s.units;
+    }
+    return used;
+}
+
+// ------------------------------------------------------------------------------------------ lists
+void CopyList::push_back(pb2_copy_t* c) {
+    c->prev = tail;
+    c->next = nullptr;
+    if (tail) tail->next = c; else head = c;
+    tail = c;
+    c->list_id = id;
+    ++count;
+}
+void CopyList::push_front(pb2_copy_t* c) {
+    c->next = head;
+    c->prev = nullptr;
+    if (head) head->prev = c; else tail = c;
+    head = c;
+    c->list_id = id;
+    ++count;
+}
+pb2_copy_t* CopyList::pop_front() {
+    pb2_copy_t* c = head;
+    if (!c) return nullptr;
+    head = c->next;
+    if (head) head->prev = nullptr; else tail = nullptr;
+    c->prev = c->next = nullptr;
+    c->list_id = 0;
+    --count;
+    return c;
+}
+void CopyList::chop(pb2_copy_t* c, CopyList* lists[3]) {
+    if (!c->list_id) return;
+    CopyList* l = lists[c->list_id];
+    if (c->prev) c->prev->next = c->next; else l->head = c->next;
+    if (c->next) c->next->prev = c->prev; else l->tail = c->prev;
+    c->prev = c->next = nullptr;
+    c->list_id = 0;
+    --l->count;
+}
+
+}  // namespace pb2
+
+// ------------------------------------------------------------------------------------------ C ABI
+extern "C" pb2_data_t* pb2_data_create(uint64_t key, uint32_t dc_id, void* host_ptr, uint32_t nb_elts) {
+    pb2_data_s* d = new pb2_data_s();
+    d->key = key;
+    d->dc_id = dc_id;
+    d->nb_elts = nb_elts;
+    d->owner_device = 0;
+    d->preferred_device = -1;
+    d->host_copy.device_index = 0;
+    d->host_copy.original = d;
+    d->host_copy.coherency_state = PB2_DATA_COHERENCY_OWNED;
+    d->host_copy.device_private = host_ptr;
+    d->host_copy.flags = PB2_FLAG_MANAGED;
+    return d;
+}
+
+extern "C" int pb2_data_copy_version(const pb2_data_t* data, int dev, uint32_t* version) {
+    if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return PB2_ERR_BAD_PARAM;
+    const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
+    if (!c) return PB2_ERR_NOT_FOUND;
+    if (version) *version = c->version;
+    return PB2_SUCCESS;
+}
+extern "C" int pb2_data_copy_coherency(const pb2_data_t* data, int dev) {
+    if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return PB2_ERR_BAD_PARAM;
+    const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
+    return c ? c->coherency_state : PB2_ERR_NOT_FOUND;
+}
+extern "C" int pb2_data_copy_readers(const pb2_data_t* data, int dev) {
+    if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return PB2_ERR_BAD_PARAM;
+    const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
+    return c ? c->readers : PB2_ERR_NOT_FOUND;
+}
+extern "C" int pb2_data_owner_device(const pb2_data_t* data) { return data ? data->owner_device : PB2_ERR_BAD_PARAM; }
+extern "C" void* pb2_data_copy_ptr(const pb2_data_t* data, int dev) {
+    if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return nullptr;
+    const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
+    return c ? c->device_private : nullptr;
+}

@@ -1,0 +1,199 @@
+// Tiled GEMM taskpool: the PTG dgemm_NN DAG unfolded over block-cyclic A, B, C and run through the device
+// module.  Host mirror of what the reference runtime does for a generated taskpool
+// (parsec_context_add_taskpool / start / wait, parsec/scheduling.c:678-806; generated hook
+// parsec/interfaces/ptg/ptg-compiler/jdf2c.c:6727-6904; complete_hook jdf2c.c:7102):
+//
+//   READ_A(m,k) : descA(m,k)   READ A -> A GEMM(m, 0..NT-1, k)          (empty body)
+//   READ_B(k,n) : descB(k,n)   READ B -> B GEMM(0..MT-1, n, k)          (empty body)
+//   GEMM(m,n,k) : descC(m,n)   READ A, READ B, RW C <- (k==0) ? descC : C GEMM(m,n,k-1)
+//                                                 -> (k==KT-1) ? descC : C GEMM(m,n,k+1)
+//                 BODY [type=CUDA dyld=parsec_b200_dgemm]
+//
+// Owner-computes: a rank runs the chains of the C tiles it owns.  The C-ABI keeps the reference's split
+// between "the hook builds a parsec_gpu_task_t" and "the device module runs it": this file only builds tasks
+// and reacts to completions, exactly like the generated code.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+
+#include "pb2_internal.h"
+#include "pb2_types.h"
+
+extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out);
+extern "C" int pb2_device_hold(pb2_device_t* dev);
+extern "C" int pb2_device_manage(pb2_device_t* dev);
+extern "C" int parsec_b200_gemm_bf16_sm100(char, char, int, int, int, float, const void*, int, const void*, int, float,
+                                           float*, int, void*);
+
+struct Geo {
+    int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id;
+};
+static Geo geo_of(const pb2_matrix_block_cyclic_t* dc) {
+    int v[12];
+    pb2_matrix_geometry(dc, v);
+    return Geo{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11]};
+}
+
+struct pb2_taskpool_s {
+    pb2_matrix_block_cyclic_t *A, *B, *C;
+    pb2_device_t* dev;
+    Geo gA, gB, gC;
+    int MT, NT, KT;
+    int64_t window = 0;  // chains in flight (0 = all)
+    int64_t panel_cols = 0;
+    std::vector<std::pair<int, int>> chains;
+    size_t next_chain = 0;
+    int64_t nb_gemm = 0, nb_read_a = 0, nb_read_b = 0;
+    int status = 0;
+};
+
+static int gemm_submit(pb2_device_t* dev, pb2_gpu_task_t* t, void* stream) {
+    (void)dev;
+    pb2_taskpool_s* tp = (pb2_taskpool_s*)t->complete_cookie;
+    const int rm = (int)t->locals[3], rn = (int)t->locals[4], rk = (int)t->locals[5];
+    int rc;
+    if (tp->gC.mtype == PB2_MATRIX_DOUBLE) {
+        rc = parsec_b200_dgemm('N', 'N', rm, rn, rk, 1.0, (const double*)t->flow_dev_ptr[0], tp->gA.mb,
+                               (const double*)t->flow_dev_ptr[1], tp->gB.mb, 1.0, (double*)t->flow_dev_ptr[2], tp->gC.mb,
+                               stream);
+    } else {
+        rc = parsec_b200_gemm_bf16_sm100('N', 'N', rm, rn, rk, 1.0f, t->flow_dev_ptr[0], tp->gA.mb, t->flow_dev_ptr[1],
+                                         tp->gB.mb, 1.0f, (float*)t->flow_dev_ptr[2], tp->gC.mb, stream);
+    }
+    return rc == PB2_SUCCESS ? PB2_HOOK_RETURN_DONE : PB2_HOOK_RETURN_ERROR;
+}
+
+static void on_complete(pb2_gpu_task_t* t, int status, void* cookie);
+
+static int spawn_gemm(pb2_taskpool_s* tp, int m, int n, int k) {
+    pb2_gpu_task_t* t = (pb2_gpu_task_t*)calloc(1, sizeof(pb2_gpu_task_t));
+    if (!t) return PB2_ERR_OUT_OF_RESOURCE;
+    t->task_type = 0;
+    t->submit = gemm_submit;
+    t->nb_flows = 3;
+    t->flow_data[0] = pb2_matrix_data_of(tp->A, m, k);
+    t->flow_data[1] = pb2_matrix_data_of(tp->B, k, n);
+    t->flow_data[2] = pb2_matrix_data_of(tp->C, m, n);
+    if (!t->flow_data[0] || !t->flow_data[1] || !t->flow_data[2]) {
+        free(t);
+        return PB2_ERR_NOT_FOUND;
+    }
+    t->flow_access[0] = PB2_FLOW_ACCESS_READ;
+    t->flow_access[1] = PB2_FLOW_ACCESS_READ;
+    t->flow_access[2] = PB2_FLOW_ACCESS_RW;
+    t->flow_nb_elts[0] = (uint32_t)((size_t)tp->gA.mb * tp->gA.nb * tp->gA.es);
+    t->flow_nb_elts[1] = (uint32_t)((size_t)tp->gB.mb * tp->gB.nb * tp->gB.es);
+    t->flow_nb_elts[2] = (uint32_t)((size_t)tp->gC.mb * tp->gC.nb * tp->gC.es);
+    t->trace_dc[0] = 0;
+    t->trace_dc[1] = 1;
+    t->trace_dc[2] = 2;
+    // pushout: only the last task of the chain writes to memory (the JDF guard k == KT-1, jdf2c.c:6839-6893)
+    t->pushout = (k == tp->KT - 1) ? (1 << 2) : 0;
+    t->priority = tp->KT - k;
+    t->locals[0] = m;
+    t->locals[1] = n;
+    t->locals[2] = k;
+    t->locals[3] = (m == tp->MT - 1) ? tp->gC.m - m * tp->gC.mb : tp->gC.mb;
+    t->locals[4] = (n == tp->NT - 1) ? tp->gC.n - n * tp->gC.nb : tp->gC.nb;
+    t->locals[5] = (k == tp->KT - 1) ? tp->gA.n - k * tp->gA.nb : tp->gA.nb;
+    t->complete = on_complete;
+    t->complete_cookie = tp;
+    int rc = pb2_kernel_scheduler(tp->dev, t);
+    return rc == PB2_HOOK_RETURN_ASYNC ? PB2_SUCCESS : PB2_ERR_DEVICE;
+}
+
+static void on_complete(pb2_gpu_task_t* t, int status, void* cookie) {
+    pb2_taskpool_s* tp = (pb2_taskpool_s*)cookie;
+    if (status != PB2_HOOK_RETURN_DONE) {
+        tp->status = status;
+        return;
+    }
+    // generated complete_hook: data_out->version++ for every WRITE flow; data_out is the host copy
+    {
+        pb2_data_s* c = t->flow_data[2];
+        std::lock_guard<std::mutex> g(c->lock);
+        c->host_copy.version++;
+    }
+    tp->nb_gemm++;
+    const int m = (int)t->locals[0], n = (int)t->locals[1], k = (int)t->locals[2];
+    if (tp->status) return;
+    if (k + 1 < tp->KT) {
+        int rc = spawn_gemm(tp, m, n, k + 1);  // release_deps: C GEMM(m,n,k) -> C GEMM(m,n,k+1)
+        if (rc) tp->status = rc;
+    } else if (tp->next_chain < tp->chains.size()) {
+        auto mn = tp->chains[tp->next_chain++];
+        int rc = spawn_gemm(tp, mn.first, mn.second, 0);
+        if (rc) tp->status = rc;
+    }
+}
+
+extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, pb2_matrix_block_cyclic_t* B,
+                                                 pb2_matrix_block_cyclic_t* C, pb2_device_t* dev) {
+    if (!A || !B || !C || !dev) return nullptr;
+    auto* tp = new pb2_taskpool_s();
+    tp->A = A; tp->B = B; tp->C = C; tp->dev = dev;
+    tp->gA = geo_of(A); tp->gB = geo_of(B); tp->gC = geo_of(C);
+    // C (M x N) += A (M x K) * B (K x N): conforming tilings on one process grid
+    bool ok = tp->gA.m == tp->gC.m && tp->gB.n == tp->gC.n && tp->gA.n == tp->gB.m && tp->gA.mb == tp->gC.mb &&
+              tp->gB.nb == tp->gC.nb && tp->gA.nb == tp->gB.mb && tp->gA.P == tp->gC.P && tp->gA.Q == tp->gC.Q &&
+              tp->gB.P == tp->gC.P && tp->gB.Q == tp->gC.Q && tp->gA.mtype == tp->gB.mtype;
+    bool types = (tp->gC.mtype == PB2_MATRIX_DOUBLE && tp->gA.mtype == PB2_MATRIX_DOUBLE) ||
+                 (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16);
+    if (!ok || !types) {
+        delete tp;
+        return nullptr;
+    }
+    tp->MT = tp->gC.mt; tp->NT = tp->gC.nt; tp->KT = tp->gA.nt;
+    return tp;
+}
+
+extern "C" int pb2_gemm_taskpool_set(pb2_taskpool_t* tp, const char* key, int64_t value) {
+    if (!tp || !key) return PB2_ERR_BAD_PARAM;
+    if (!strcmp(key, "window")) tp->window = value;
+    else if (!strcmp(key, "panel_cols")) tp->panel_cols = value;
+    else return PB2_ERR_NOT_FOUND;
+    return PB2_SUCCESS;
+}
+
+extern "C" void pb2_gemm_taskpool_free(pb2_taskpool_t* tp) { delete tp; }
+
+extern "C" int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats) {
+    if (!tp) return PB2_ERR_BAD_PARAM;
+    if (tp->gC.P * tp->gC.Q != 1) {
+        fprintf(stderr, "[parsec_b200] multi-rank taskpools run through pb2_gemm_taskpool_run_dist (comm_nccl.cu)\n");
+        return PB2_ERR_NOT_SUPPORTED;
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    tp->nb_gemm = tp->nb_read_a = tp->nb_read_b = 0;
+    tp->status = 0;
+    tp->chains.clear();
+    tp->next_chain = 0;
+    // startup tasks: READ_A / READ_B have empty bodies and only forward the collection's tile
+    tp->nb_read_a = (int64_t)tp->MT * tp->KT;
+    tp->nb_read_b = (int64_t)tp->KT * tp->NT;
+    // chain activation order: column panels of C so that finished tiles leave while later panels compute
+    for (int n = 0; n < tp->NT; ++n)
+        for (int m = 0; m < tp->MT; ++m) tp->chains.push_back({m, n});
+    int64_t w = tp->window > 0 ? tp->window : (int64_t)tp->chains.size();
+    if (!pb2_device_hold(tp->dev)) return PB2_ERROR;  // somebody else is driving this device
+    while (tp->next_chain < tp->chains.size() && (int64_t)tp->next_chain < w) {
+        auto mn = tp->chains[tp->next_chain++];
+        int rc = spawn_gemm(tp, mn.first, mn.second, 0);
+        if (rc) {
+            tp->status = rc;
+            break;
+        }
+    }
+    int rc = pb2_device_manage(tp->dev);  // add_taskpool + start + wait
+    if (rc != PB2_SUCCESS && !tp->status) tp->status = rc;
+    auto t1 = std::chrono::steady_clock::now();
+    if (stats) {
+        stats->nb_gemm = tp->nb_gemm;
+        stats->nb_read_a = tp->nb_read_a;
+        stats->nb_read_b = tp->nb_read_b;
+        stats->seconds = std::chrono::duration<double>(t1 - t0).count();
+    }
+    return tp->status ? PB2_ERROR : PB2_SUCCESS;
+}

@@ -1,0 +1,94 @@
+// Internal C++ types behind the opaque handles of include/parsec_b200.h.
+#ifndef PB2_TYPES_H
+#define PB2_TYPES_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <deque>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "parsec_b200.h"
+
+#define PB2_XFER_NONE 0
+#define PB2_XFER_UNDER 1
+#define PB2_XFER_COMPLETE 2
+
+#define PB2_FLAG_OWNED 0x80   /* PARSEC_DATA_FLAG_PARSEC_OWNED: the module allocated the device memory */
+#define PB2_FLAG_MANAGED 0x40 /* PARSEC_DATA_FLAG_PARSEC_MANAGED */
+
+// parsec_data_copy_t (parsec/data_internal.h:57-81)
+struct pb2_copy_t {
+    pb2_copy_t* prev = nullptr;  // LRU list links (parsec_list_item_t super)
+    pb2_copy_t* next = nullptr;
+    int list_id = 0;             // 0 = none, 1 = gpu_mem_lru, 2 = gpu_mem_owned_lru
+    int8_t device_index = 0;
+    uint8_t flags = 0;
+    uint8_t coherency_state = PB2_DATA_COHERENCY_INVALID;
+    uint8_t data_transfer_status = PB2_XFER_NONE;
+    int32_t readers = 0;
+    uint32_t version = 0;
+    pb2_data_s* original = nullptr;
+    void* device_private = nullptr;
+    uint64_t ready_seq = 0;      // h2d-stream sequence number after which the device bytes are valid
+    cudaEvent_t ready_event = nullptr;  // non-null when validity comes from another stream (NCCL)
+};
+
+// parsec_data_t (parsec/data_internal.h:35-55)
+struct pb2_data_s {
+    std::mutex lock;
+    uint64_t key = 0;
+    uint32_t dc_id = 0;
+    int8_t owner_device = 0;
+    int8_t preferred_device = -1;
+    uint32_t nb_elts = 0;
+    pb2_copy_t host_copy;
+    pb2_copy_t* device_copies[PB2_MAX_DEVICES] = {nullptr};
+};
+
+namespace pb2 {
+
+// data.c:319-433 / :299-317 -- implemented in data.cu
+int data_start_transfer_ownership(pb2_data_s* data, int device, uint8_t access);
+void data_end_transfer_ownership(pb2_data_s* data, int device, uint8_t access);
+
+// HBM heap: first-fit over fixed-size units, same policy as parsec/utils/zone_malloc.c
+class ZoneHeap {
+public:
+    ZoneHeap(char* base, int max_segment, size_t unit);
+    void* alloc(size_t size);
+    bool free(void* p);
+    size_t in_use() const;
+    size_t capacity() const { return unit_ * (size_t)nseg_; }
+    char* base() const { return base_; }
+    int64_t offset_of(const void* p) const { return (const char*)p - base_; }
+
+private:
+    struct Seg {
+        int busy, units, before;
+    };
+    Seg* at(int id) { return (id < 0 || id >= nseg_) ? nullptr : &seg_[id]; }
+    char* base_;
+    std::vector<Seg> seg_;
+    int nseg_, cursor_;
+    size_t unit_;
+};
+
+struct CopyList {  // parsec_list_t of data copies, LRU order: front = oldest
+    pb2_copy_t* head = nullptr;
+    pb2_copy_t* tail = nullptr;
+    int id;
+    size_t count = 0;
+    explicit CopyList(int id_) : id(id_) {}
+    void push_back(pb2_copy_t* c);
+    void push_front(pb2_copy_t* c);
+    pb2_copy_t* pop_front();
+    static void chop(pb2_copy_t* c, CopyList* lists[3]);
+};
+
+}  // namespace pb2
+
+#endif

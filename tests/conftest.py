@@ -22,3 +22,16 @@ def _built():
     if not os.path.exists(lib) and os.path.exists("/usr/local/cuda/bin/nvcc"):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "parsec-1_b200"), "-j8"])
     yield
+
+
+def load_hostapi():
+    """Import parsec-1_b200/hostapi.py (the directory name is not a valid module name)."""
+    import importlib.util
+    name = "parsec1_b200_hostapi"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "parsec-1_b200", "hostapi.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod

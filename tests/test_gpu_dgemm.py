@@ -1,0 +1,101 @@
+"""Tile kernel parity: parsec_b200_dgemm_sm100 (through the C ABI) against the oracle's tile GEMM."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import load_hostapi
+
+pytestmark = pytest.mark.gpu
+H = load_hostapi()
+EPS = 2.0 ** -53
+
+
+def _run(transa, transb, m, n, k, alpha, beta, seed=0, lda_pad=0):
+    import torch
+    rng = np.random.default_rng(seed)
+    opA = rng.uniform(-0.5, 0.5, (m, k))
+    opB = rng.uniform(-0.5, 0.5, (k, n))
+    Cm = np.asfortranarray(rng.uniform(-0.5, 0.5, (m, n)))
+    A = np.asfortranarray(opA if transa == "N" else opA.T)
+    B = np.asfortranarray(opB if transb == "N" else opB.T)
+    lda, ldb, ldc = A.shape[0] + lda_pad, B.shape[0] + lda_pad, m + lda_pad
+
+    def to_dev(X, ld):  # column-major with leading dimension ld
+        buf = np.zeros((X.shape[1], ld))
+        buf[:, :X.shape[0]] = X.T
+        return torch.from_numpy(buf).cuda()
+
+    dA, dB, dC = to_dev(A, lda), to_dev(B, ldb), to_dev(Cm, ldc)
+    rc = H.dgemm(transa, transb, m, n, k, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dC.data_ptr(), ldc,
+                 torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    got = dC.cpu().numpy()[:, :m].T
+    want = np.asfortranarray(Cm.copy())
+    O.dgemm_tile(alpha, np.asfortranarray(opA), np.asfortranarray(opB), beta, want)
+    # north-star norm with N := k (the contraction length of this tile product)
+    inf = lambda X: np.abs(X).sum(axis=1).max()
+    denom = max(inf(opA) * inf(opB) * max(k, 1) * EPS, 1e-300)
+    return inf(got - want) / denom, got, want
+
+
+@pytest.mark.parametrize("n", [128, 256, 512, 1024])
+def test_square_tiles_nn(n):
+    r, _, _ = _run("N", "N", n, n, n, 1.0, 1.0, seed=n)
+    assert r < 10
+
+
+@pytest.mark.parametrize("m,n,k", [(1, 1, 1), (40, 40, 40), (240, 200, 40), (129, 127, 17), (128, 256, 48),
+                                   (1000, 24, 8), (130, 130, 2048), (256, 128, 16)])
+def test_ragged_shapes(m, n, k):
+    r, _, _ = _run("N", "N", m, n, k, 1.0, 1.0, seed=m + n + k)
+    assert r < 10
+
+
+@pytest.mark.parametrize("alpha,beta", [(0.0, 1.0), (1.0, 0.0), (-2.5, 0.5), (1.0, 2.0)])
+def test_alpha_beta(alpha, beta):
+    """alpha = 0, beta = 1 is what nvlink.jdf / stress.jdf use (C must come back unchanged)."""
+    r, got, want = _run("N", "N", 256, 256, 256, alpha, beta, seed=3)
+    assert r < 10
+    if alpha == 0.0 and beta == 1.0:
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("ta,tb", [("T", "N"), ("N", "T"), ("T", "T")])
+def test_transposes(ta, tb):
+    r, _, _ = _run(ta, tb, 96, 160, 72, 1.0, 1.0, seed=5)
+    assert r < 10
+
+
+def test_padded_leading_dimensions_and_odd_ld():
+    assert _run("N", "N", 256, 128, 64, 1.0, 1.0, seed=7, lda_pad=6)[0] < 10   # even ld: TMA path
+    assert _run("N", "N", 256, 128, 64, 1.0, 1.0, seed=8, lda_pad=3)[0] < 10   # odd ld: generic path
+
+
+def test_bad_arguments_are_rejected():
+    import torch
+    x = torch.zeros(64, dtype=torch.float64, device="cuda")
+    p = x.data_ptr()
+    assert H.dgemm("X", "N", 8, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8) == -4
+    assert H.dgemm("N", "N", -1, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8) == -4
+    assert H.dgemm("N", "N", 8, 8, 8, 1.0, p, 4, p, 8, 1.0, p, 8) == -4   # lda < m
+    assert H.dgemm("N", "N", 0, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8) == 0    # empty: nothing to do
+
+
+def test_linearity_at_full_tile_size():
+    """Size-independent property at the BASELINE tile size: (A1 + A2) B == A1 B + A2 B up to rounding."""
+    import torch
+    n = 1024
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A1 = torch.rand(n, n, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    A2 = torch.rand(n, n, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    B = torch.rand(n, n, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    s = torch.cuda.current_stream().cuda_stream
+    outs = []
+    for A in (A1, A2, A1 + A2):
+        Cm = torch.zeros(n, n, dtype=torch.float64, device="cuda")
+        assert H.dgemm("N", "N", n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, Cm.data_ptr(), n, s) == 0
+        outs.append(Cm)
+    torch.cuda.synchronize()
+    err = (outs[0] + outs[1] - outs[2]).abs().max().item()
+    assert err < 1e-11
