@@ -24,6 +24,7 @@ extern "C" {
 #define PB2_ERR_NOT_FOUND (-3)
 #define PB2_ERR_BAD_PARAM (-4)
 #define PB2_ERR_NOT_SUPPORTED (-7)
+#define PB2_ERR_VALUE_OUT_OF_BOUNDS (-8)
 #define PB2_ERR_DEVICE (-10)
 
 #define PB2_HOOK_RETURN_DONE 0
@@ -233,6 +234,14 @@ int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* de
  * GPU for every local tile of `dc` and written to dc->mat (fp64) or, for PB2_MATRIX_BF16 / FLOAT, rounded from
  * the same values.  Used by bench.py; bit-exact with the CPU generator. */
 int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev);
+/* Same result as pb2_matrix_fill_lcg, for callers that must not allocate device memory: code that runs after
+ * pb2_device_create has handed 95 % of HBM to the tile heap (a staging cudaMalloc may then fail), or while the
+ * pipeline is busy (cudaMalloc / cudaFree synchronise the device).  Has no counterpart in the reference.
+ * Tiles are staged through a 16 MiB buffer that is part of the library image on every GPU that loads it, so one tile
+ * may be at most 16 MiB; larger tiles return PB2_ERR_VALUE_OUT_OF_BOUNDS (-8).  The first call on a device resolves
+ * the buffer's address and should come before any stream capture.  All calls on a device share that buffer (it keeps
+ * the previous call's bytes; nothing needs it zeroed), so calls that overlap on one GPU race: serialise them. */
+int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev);
 
 /* ------------------------------------------------------------------------------------------------
  * Tiled GEMM taskpool: the PTG dgemm_NN DAG (READ_A, READ_B, GEMM(m,n,k) with the C chain over k) unfolded over

@@ -211,3 +211,102 @@ extern "C" int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed,
     cudaFree(dcoords);
     return rc;
 }
+
+// ------------------------------------------------------------------------------------ generator, no allocation
+// pb2_matrix_fill_lcg above stages tiles through a cudaMalloc'd buffer.  That is a problem for two kinds of callers
+// of this library:
+//   * anything that runs after pb2_device_create: the device module has by then taken 95 % of the free HBM for its
+//     tile heap, so a further cudaMalloc of a staging buffer can fail with out-of-memory on a perfectly healthy run;
+//   * anything that runs while the pipeline is busy: cudaMalloc/cudaFree synchronise the whole device, which stalls
+//     every stream the manager is driving.
+// The variant below therefore owns its staging space statically.  The array lives in every GPU context that loads
+// this library until the process exits, so it is kept modest: 16 MiB, i.e. tiles of at most 16 MiB (NB = 1024 fp64 is
+// 8 MiB; NB = 2048 fp64 does not fit and is refused).
+#define PB2_FILL_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) unsigned char pb2_fill_scratch[PB2_FILL_SCRATCH_BYTES];
+
+// In host code `pb2_fill_scratch` is only a handle for the symbol, not a device address; the address has to be asked
+// for once per device, with that device current.
+static void* g_fill_scratch_addr[64] = {nullptr};
+
+static int fill_scratch_address(int cuda_index, void** out) {
+    if (cuda_index < 0 || cuda_index >= 64) return PB2_ERR_BAD_PARAM;
+    if (!g_fill_scratch_addr[cuda_index]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, pb2_fill_scratch);
+        if (e != cudaSuccess || !p) {
+            fprintf(stderr, "[parsec_b200] cudaGetSymbolAddress(pb2_fill_scratch) failed on device %d: %s\n", cuda_index,
+                    cudaGetErrorString(e));
+            return PB2_ERR_DEVICE;
+        }
+        g_fill_scratch_addr[cuda_index] = p;
+    }
+    *out = g_fill_scratch_addr[cuda_index];
+    return PB2_SUCCESS;
+}
+
+// Same arithmetic as lcg_fill_tiles; the tile coordinates are derived from the storage position instead of being read
+// from a coordinate table (which would be one more buffer to allocate).
+template <typename T>
+__global__ void lcg_fill_tiles_by_position(T* out, long long first_pos, int nb_elem_r, int P, int Q, int rrank, int crank,
+                                           int mb, int nb, int M, unsigned seed) {
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= nb) return;
+    const long long pos = first_pos + blockIdx.y;
+    const int m = (int)(pos % nb_elem_r) * P + rrank;
+    const int n = (int)(pos / nb_elem_r) * Q + crank;
+    unsigned long long jump = (unsigned long long)m + ((unsigned long long)n + (unsigned long long)col) * (unsigned long long)M;
+    unsigned long long x = lcg_jump(jump, seed);
+    T* p = out + (size_t)blockIdx.y * mb * nb + (size_t)col * mb;
+    for (int row = 0; row < mb; ++row) {
+        float scaled = __fmul_rn(__ull2float_rn(x), 5.4210108624275222e-20f);
+        p[row] = from_f32<T>(__fsub_rn(0.5f, scaled));
+        x = PB2_RND_A * x + PB2_RND_C;
+    }
+}
+
+// Fills every local tile of `dc` like pb2_matrix_fill_lcg, without allocating anything (no cudaMalloc / cudaFree, no
+// host heap, no library call that allocates): tiles are generated into the static scratch and copied to dc->mat.
+//   * The first call on a device looks up the scratch address (cudaGetSymbolAddress); make that first call before
+//     starting any stream capture.
+//   * One tile must fit in the 16 MiB scratch; larger tiles return PB2_ERR_VALUE_OUT_OF_BOUNDS with a message.
+//   * Every call on a device reuses the same scratch and finds the previous call's bytes in it.  Nothing here needs
+//     zero-initialised scratch: each launch overwrites exactly the bytes that are then copied out.  Two calls that
+//     overlap on the same GPU (different host threads) would race on it -- serialise them.
+extern "C" int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev) {
+    if (!dc || !dc->mat || !dev) return PB2_ERR_BAD_PARAM;
+    if (dc->i != 0 || dc->j != 0) return PB2_ERR_NOT_SUPPORTED;  // sub-matrix views: use pb2_matrix_fill_lcg
+    const size_t tile_bytes = (size_t)dc->bsiz * dc->elem_size;
+    if (tile_bytes > PB2_FILL_SCRATCH_BYTES) {
+        fprintf(stderr,
+                "[parsec_b200] pb2_matrix_fill_lcg_noalloc: a %d x %d tile is %zu bytes, the static scratch holds %u; "
+                "use pb2_matrix_fill_lcg for tiles this large\n",
+                dc->mb, dc->nb, tile_bytes, PB2_FILL_SCRATCH_BYTES);
+        return PB2_ERR_VALUE_OUT_OF_BOUNDS;
+    }
+    const int cuda_index = pb2_device_cuda_index(dev);
+    if (cudaSetDevice(cuda_index) != cudaSuccess) return PB2_ERR_DEVICE;
+    void* scratch = nullptr;
+    int rc = fill_scratch_address(cuda_index, &scratch);
+    if (rc != PB2_SUCCESS) return rc;
+    const long long batch = (long long)(PB2_FILL_SCRATCH_BYTES / tile_bytes);
+    for (long long t0 = 0; t0 < dc->nb_local_tiles; t0 += batch) {
+        const int nt = (int)std::min<long long>(batch, dc->nb_local_tiles - t0);
+        dim3 grid((dc->nb + 127) / 128, nt);
+        if (dc->mtype == PB2_MATRIX_DOUBLE)
+            lcg_fill_tiles_by_position<double><<<grid, 128>>>((double*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->rrank,
+                                                              dc->crank, dc->mb, dc->nb, dc->m, seed);
+        else if (dc->mtype == PB2_MATRIX_FLOAT)
+            lcg_fill_tiles_by_position<float><<<grid, 128>>>((float*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->rrank,
+                                                             dc->crank, dc->mb, dc->nb, dc->m, seed);
+        else
+            lcg_fill_tiles_by_position<__nv_bfloat16><<<grid, 128>>>((__nv_bfloat16*)scratch, t0, dc->nb_elem_r, dc->P,
+                                                                     dc->Q, dc->rrank, dc->crank, dc->mb, dc->nb, dc->m,
+                                                                     seed);
+        if (cudaGetLastError() != cudaSuccess) return PB2_ERR_DEVICE;
+        if (cudaMemcpy((char*)dc->mat + (size_t)t0 * tile_bytes, scratch, tile_bytes * nt, cudaMemcpyDeviceToHost) !=
+            cudaSuccess)
+            return PB2_ERR_DEVICE;
+    }
+    return PB2_SUCCESS;
+}

@@ -102,6 +102,7 @@ def lib():
         "pb2_matrix_position": (i64, [vp, i32, i32]), "pb2_matrix_data_key": (u64, [vp, i32, i32]),
         "pb2_matrix_data_of": (vp, [vp, i32, i32]), "pb2_matrix_register_memory": (i32, [vp, vp]),
         "pb2_matrix_unregister_memory": (i32, [vp, vp]), "pb2_matrix_fill_lcg": (i32, [vp, C.c_uint, vp]),
+        "pb2_matrix_fill_lcg_noalloc": (i32, [vp, C.c_uint, vp]),
         "pb2_gemm_taskpool_new": (vp, [vp, vp, vp, vp]), "pb2_gemm_taskpool_set": (i32, [vp, C.c_char_p, i64]),
         "pb2_gemm_taskpool_run": (i32, [vp, C.POINTER(GemmStats)]), "pb2_gemm_taskpool_free": (None, [vp]),
     }
