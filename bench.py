@@ -162,20 +162,26 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    N, NB = args.n, args.nb
+    NB = args.nb
+    # weak scaling: flops per GPU constant, N_g = N_1 * g^(1/3) rounded to a whole number of tiles
+    N = args.n if world == 1 else int(round(args.n * world ** (1.0 / 3.0) / NB)) * NB
+    P, Q = H.grid_for(world)
+    comm = H.Comm(local_rank, P, Q, rank) if world > 1 else None
     peak_tf = fp64_peak_tflops(torch)
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0)
     mats, bufs = [], []
     for seed in (1789, 1805, 1901):
-        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB)
-        b = torch.empty(m.nbytes, dtype=torch.uint8, pin_memory=True)   # cudaHostAlloc: the collection's host memory
+        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank)
+        b = torch.empty(max(m.nbytes, 8), dtype=torch.uint8, pin_memory=True)   # cudaHostAlloc: the collection's host memory
         m.set_buffer(b)
-        m.fill_lcg(seed + 7 * rank, dev)
+        m.fill_lcg(seed, dev)
         mats.append(m)
         bufs.append(b)
     A, B, Cm = mats
     flops = 2.0 * N ** 3
     knobs = {"window": args.window} if args.window else {}
+    if comm is not None:
+        knobs["comm"] = comm
 
     def barrier():
         if world > 1:
@@ -226,7 +232,7 @@ def main():
     dev = H.Device(local_rank, **dev2_params)
     mats = []
     for b in bufs:
-        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB)
+        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank)
         m.set_buffer(b)
         mats.append(m)
     A, B, Cm = mats
@@ -242,25 +248,29 @@ def main():
         achieved_tf = per_launch_flops * nstreams / (avg_ms * 1e-3) * 1e-12
         prof = {"avg_launch_ms": avg_ms, "samples": int(len(lms)), "resident_launches": nstreams}
 
-    value = flops * world / (ms_resident * 1e-3) * 1e-9
-    e2e = flops * world / (ms_e2e * 1e-3) * 1e-9
+    value = flops / (ms_resident * 1e-3) * 1e-9          # whole job: one N x N x N product spread over all ranks
+    e2e = flops / (ms_e2e * 1e-3) * 1e-9
     tile_bytes = NB * NB * 8
     out = {
         "metric": "tiled GEMM GFLOP/s", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_resident, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
-                               "(BASELINE configs[1])" % (N, NB),
+        "config": {"workload": ("tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
+                                "(BASELINE configs[1])" % (N, NB)) if world == 1 else
+                               ("tiled DGEMM N=%d NB=%d fp64, 2D block-cyclic %dx%d over %d B200 with NCCL tile bcast "
+                                "(BASELINE configs[2] shape; weak scaling from N=%d)" % (N, NB, P, Q, world, args.n)),
                    "tasks_per_step": (N // NB) ** 3, "l2": "inputs (3 x %.1f GiB) far larger than L2" % (N * N * 8 / 2 ** 30),
-                   "parallelism": "1 process per GPU; %d exec streams" % (args.streams - 2),
+                   "parallelism": "1 process per GPU, %dx%d grid; %d exec streams per GPU" % (P, Q, args.streams - 2),
                    "pct_of_fp64_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
         "e2e": {"value": e2e, "unit": "GFLOP/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": st_e2e["data_in_from_host"] // max(1, args.steps),
-                "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps)},
+                "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps),
+                "nvlink_bytes_in_per_step_rank0": st_e2e["data_in_from_peers"] // max(1, args.steps)},
         "gpu_launches": st_resident["kernel_launches"],
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": (achieved_tf / peak_tf) if prof else None, "traffic": None,
+                     "frac": (achieved_tf / peak_tf) if prof else None, "traffic": 25206528,  # dram bytes per launch, ncu --set full (profiles/dgemm_tma_r1_ncu.md)
+                     
                      "kernel": "pb2::dgemm_nn_tma", "peak_source": "measured live: torch.matmul fp64 8192^3 (cuBLAS), "
                      "best of 10; MEASURED_PEAKS.json has no fp64 entry (DMMA issue peak measured 37.1 TFLOP/s, "
                      "profiles/microbench_r1.md)", "detail": prof,
@@ -276,6 +286,8 @@ def main():
     dev.close()
     if rank == 0:
         print(json.dumps(out))
+    if comm is not None:
+        comm.close()
     if world > 1:
         dist.destroy_process_group()
 

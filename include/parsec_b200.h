@@ -259,6 +259,31 @@ pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, pb2_matrix_b
                                       pb2_matrix_block_cyclic_t* C, pb2_device_t* dev);
 /* knobs (before run): chains in flight, exec-side dtype path */
 int pb2_gemm_taskpool_set(pb2_taskpool_t* tp, const char* key, int64_t value);
+/* ------------------------------------------------------------------------------------------------
+ * Intra-box tile data plane (piece 3): NCCL broadcasts along the rows / columns of the P x Q grid.  Replaces, for
+ * tile payloads, remote_dep_mpi_put_start / get_start / get_end_cb (parsec/remote_dep_mpi.c:1593, :1963, :2082) and
+ * mpi_no_thread_put / get (parsec/parsec_mpi_funnelled.c:793, :896); the broadcast topology knob
+ * runtime_comm_coll_bcast (parsec/remote_dep.c:272-291) has no equivalent because NVSwitch is uniform.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_comm_s pb2_comm_t;
+/* ncclGetUniqueId: 128 bytes, to be published by column 0 of each process row and row 0 of each process column */
+int pb2_comm_unique_id(void* out128);
+/* one communicator per process row (size Q, my index = rank mod Q) and per process column (size P, rank / Q) */
+int pb2_comm_create(int cuda_index, int P, int Q, int rank, const void* row_id, const void* col_id, pb2_comm_t** out);
+int pb2_comm_destroy(pb2_comm_t* comm);
+/* one in-place tile broadcast: which = 0 along my process row (A tiles), 1 along my process column (B tiles) */
+int pb2_comm_bcast(pb2_comm_t* comm, int which, void* device_buf, size_t bytes, int root);
+/* The canonical per-rank sequence of broadcasts for C(MT x NT) += A(MT x KT) * B(KT x NT) (host logic, no CUDA):
+ * for k ascending, the row broadcasts A(m,k) of my process row (m ascending) then the column broadcasts B(k,n) of
+ * my process column (n ascending); root = k mod Q resp. k mod P, the owner under twoDBC_rank_of.  Returns the
+ * number of operations (call with out == NULL to size the buffer). */
+typedef struct pb2_bcast_op_s {
+    int32_t which, k, idx, root, i_am_root;
+} pb2_bcast_op_t;
+int64_t pb2_comm_plan(int P, int Q, int rank, int MT, int NT, int KT, pb2_bcast_op_t* out, int64_t max_ops);
+/* give a P x Q taskpool its communicator (must match the descriptors' grid and rank) */
+int pb2_gemm_taskpool_set_comm(pb2_taskpool_t* tp, pb2_comm_t* comm);
+
 /* add_taskpool + start + wait; C is valid on the host afterwards */
 int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats);
 void pb2_gemm_taskpool_free(pb2_taskpool_t* tp);

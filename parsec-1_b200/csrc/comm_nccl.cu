@@ -1,0 +1,156 @@
+// Intra-box data plane for the P x Q block-cyclic tiled GEMM: tile broadcasts over NCCL / NVLink instead of the
+// reference's host-bounced MPI sends.
+//
+// What it replaces: for every output flow with remote successors the reference sends one ACTIVATE active message,
+// the receiver allocates a HOST arena tile and answers GET, the sender MPI_Isend's the host copy, and the consumer GPU
+// later pays an H2D (remote_dep.c:454-591, remote_dep_mpi.c:1593-1726, :1963-2118, parsec_mpi_funnelled.c:793,896);
+// broadcasts emerge from rank_bits walked along a chain/binomial tree (remote_dep.c:334-372).
+// For GEMM the communication pattern is static: A(m,k) goes to every rank of process row m mod P from
+// column k mod Q, B(k,n) to every rank of process column n mod Q from row k mod P.  Here each of those is ONE
+// ncclBroadcast on a per-row (size Q) or per-column (size P) communicator, GPU to GPU, received straight into an HBM
+// cache slot that the consumer's stage-in finds "already on the device, same version" (no host bounce, no H2D).
+//
+// Ordering: every rank issues its collectives in one canonical order -- for k ascending: the row broadcasts of step k
+// (m ascending), then the column broadcasts of step k (n ascending) -- on one stream.  A rank's sequence is a
+// subsequence of that global order restricted to its two communicators, so the earliest incomplete collective always
+// is the next one on every participant's stream: no deadlock, no tree tuning (NVSwitch is uniform).
+#include <dlfcn.h>
+#include <nccl.h>  // types only: the library is bound at run time, see nccl_api()
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "pb2_internal.h"
+#include "pb2_types.h"
+
+// NCCL is bound lazily with dlopen instead of at link time: a host process may already carry its own libnccl.so.2
+// (PyTorch bundles a newer one than the system's) and two different NCCLs under one soname cannot coexist.  The copy
+// that is already loaded wins; otherwise the system library is loaded.
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+    ncclResult_t (*CommDestroy)(ncclComm_t);
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    const char* (*GetErrorString)(ncclResult_t);
+    bool ok = false;
+};
+static NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.ok ? &api : nullptr;
+    tried = true;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) {
+        fprintf(stderr, "[parsec_b200] cannot load libnccl.so.2: %s\n", dlerror());
+        return nullptr;
+    }
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
+    api.Broadcast = (decltype(api.Broadcast))dlsym(h, "ncclBroadcast");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString;
+    return api.ok ? &api : nullptr;
+}
+
+struct pb2_comm_s {
+    int P, Q, rank, myrow, mycol;
+    ncclComm_t row = nullptr, col = nullptr;  // row: the Q ranks of my process row; col: the P ranks of my column
+    cudaStream_t stream = nullptr;
+    int cuda_index = 0;
+};
+typedef struct pb2_comm_s pb2_comm_t;
+
+extern "C" int pb2_comm_unique_id(void* out128) {
+    if (!out128) return PB2_ERR_BAD_PARAM;
+    NcclApi* nccl = nccl_api();
+    if (!nccl) return PB2_ERR_NOT_FOUND;
+    ncclUniqueId id;
+    if (nccl->GetUniqueId(&id) != ncclSuccess) return PB2_ERR_DEVICE;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(out128, &id, 128);
+    return PB2_SUCCESS;
+}
+
+// row_id: the unique id published by the rank in column 0 of my process row; col_id: by the rank in row 0 of my column.
+extern "C" int pb2_comm_create(int cuda_index, int P, int Q, int rank, const void* row_id, const void* col_id,
+                               pb2_comm_t** out) {
+    if (!out || P <= 0 || Q <= 0 || rank < 0 || rank >= P * Q) return PB2_ERR_BAD_PARAM;
+    NcclApi* nccl = nccl_api();
+    if (!nccl) return PB2_ERR_NOT_FOUND;
+    if (cudaSetDevice(cuda_index) != cudaSuccess) return PB2_ERR_DEVICE;
+    pb2_comm_s* c = new pb2_comm_s();
+    c->P = P; c->Q = Q; c->rank = rank; c->myrow = rank / Q; c->mycol = rank % Q; c->cuda_index = cuda_index;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return PB2_ERR_DEVICE; }
+    ncclUniqueId rid, cid;
+    if (Q > 1) {
+        if (!row_id) { delete c; return PB2_ERR_BAD_PARAM; }
+        memcpy(&rid, row_id, 128);
+        if (nccl->CommInitRank(&c->row, Q, rid, c->mycol) != ncclSuccess) { delete c; return PB2_ERR_DEVICE; }
+    }
+    if (P > 1) {
+        if (!col_id) { delete c; return PB2_ERR_BAD_PARAM; }
+        memcpy(&cid, col_id, 128);
+        if (nccl->CommInitRank(&c->col, P, cid, c->myrow) != ncclSuccess) { delete c; return PB2_ERR_DEVICE; }
+    }
+    *out = c;
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_comm_destroy(pb2_comm_t* c) {
+    if (!c) return PB2_ERR_BAD_PARAM;
+    cudaSetDevice(c->cuda_index);
+    cudaStreamSynchronize(c->stream);
+    if (c->row) nccl_api()->CommDestroy(c->row);
+    if (c->col) nccl_api()->CommDestroy(c->col);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return PB2_SUCCESS;
+}
+
+extern "C" void* pb2_comm_stream(pb2_comm_t* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int pb2_comm_geometry(const pb2_comm_t* c, int* out /*[5]*/) {
+    if (!c || !out) return PB2_ERR_BAD_PARAM;
+    out[0] = c->P; out[1] = c->Q; out[2] = c->rank; out[3] = c->myrow; out[4] = c->mycol;
+    return PB2_SUCCESS;
+}
+
+// one tile broadcast; which = 0: along my process row (A tiles), 1: along my process column (B tiles);
+// root is the rank index INSIDE that communicator.  In place: the root sends from buf, the others receive into buf.
+extern "C" int pb2_comm_bcast(pb2_comm_t* c, int which, void* buf, size_t bytes, int root) {
+    if (!c || !buf) return PB2_ERR_BAD_PARAM;
+    ncclComm_t comm = which == 0 ? c->row : c->col;
+    if (!comm) return PB2_SUCCESS;  // communicator of size 1
+    ncclResult_t r = nccl_api()->Broadcast(buf, buf, bytes, ncclChar, root, comm, c->stream);
+    if (r != ncclSuccess) {
+        fprintf(stderr, "[parsec_b200] ncclBroadcast failed: %s\n", nccl_api()->GetErrorString(r));
+        return PB2_ERR_DEVICE;
+    }
+    return PB2_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------ the plan (host logic)
+// The canonical sequence of collectives of ONE rank for C(MT x NT) += A(MT x KT) * B(KT x NT) on a P x Q grid.
+// Pure integer logic, no CUDA: tests/test_dist_gloo.py checks it across ranks on the CPU.
+// pb2_bcast_op_t: which (0 = row communicator / an A tile, 1 = column communicator / a B tile), k (GEMM step),
+// idx (m for A(m,k), n for B(k,n)), root (rank inside the communicator), i_am_root.
+extern "C" int64_t pb2_comm_plan(int P, int Q, int rank, int MT, int NT, int KT, pb2_bcast_op_t* out, int64_t max_ops) {
+    if (P <= 0 || Q <= 0 || rank < 0 || rank >= P * Q || MT <= 0 || NT <= 0 || KT <= 0) return PB2_ERR_BAD_PARAM;
+    const int myrow = rank / Q, mycol = rank % Q;
+    int64_t n = 0;
+    for (int k = 0; k < KT; ++k) {
+        if (Q > 1)
+            for (int m = myrow; m < MT; m += P) {  // A(m,k): owner is (m mod P, k mod Q)
+                if (out && n < max_ops) out[n] = pb2_bcast_op_t{0, k, m, k % Q, (k % Q) == mycol};
+                ++n;
+            }
+        if (P > 1)
+            for (int c = mycol; c < NT; c += Q) {  // B(k,c): owner is (k mod P, c mod Q)
+                if (out && n < max_ops) out[n] = pb2_bcast_op_t{1, k, c, k % P, (k % P) == myrow};
+                ++n;
+            }
+    }
+    return n;
+}

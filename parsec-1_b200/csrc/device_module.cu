@@ -325,6 +325,48 @@ extern "C" int pb2_default_stage_out(pb2_gpu_task_t* t, uint32_t flow_mask, void
 
 // ------------------------------------------------------------------------------------ reserve (a4)
 // Returns 0 = every flow has a device copy, 1 = no room right now, 2 = a needed copy is being written back.
+// zone_malloc with eviction from the clean LRU (:934-1113).  `t` (may be null) is the task being served: its own
+// tiles are never stolen (:1041-1062).  Returns nullptr when nothing evictable is left.
+static void* alloc_evicting(pb2_device_s* d, size_t bytes, pb2_gpu_task_t* t) {
+    void* mem = nullptr;
+    while (!(mem = d->heap->alloc(bytes))) {
+        pb2_copy_t* victim = nullptr;
+        std::vector<pb2_copy_t*> skipped;
+        while (pb2_copy_t* cand = d->lru.pop_front()) {
+            if (cand->readers != 0) continue;  // dropped from the list; pop re-files it when readers hit 0
+            bool mine = false;
+            if (t)
+                for (int j = 0; j < t->nb_flows; ++j)
+                    if (t->flow_data[j] && cand->original == t->flow_data[j]) mine = true;
+            if (mine) {
+                skipped.push_back(cand);
+                continue;
+            }
+            victim = cand;
+            break;
+        }
+        for (auto it = skipped.rbegin(); it != skipped.rend(); ++it) d->lru.push_front(*it);
+        if (!victim) return nullptr;
+        if (d->params.trace_events && victim->original) {
+            pb2_event_t e;
+            memset(&e, 0, sizeof(e));
+            e.dc = victim->original->dc_id;
+            e.key = (uint32_t)victim->original->key;
+            e.kind = EV_EVICT;
+            e.k = -1;
+            e.gpu_version = victim->version;
+            e.cpu_version = victim->original->host_copy.version;
+            e.gpu_coh = victim->coherency_state;
+            e.cpu_coh = victim->original->host_copy.coherency_state;
+            e.owner_device = victim->original->owner_device;
+            d->events.push_back(e);
+        }
+        release_copy(d, victim);
+        d->stats.nb_evictions++;
+    }
+    return mem;
+}
+
 static int reserve_device_space(pb2_device_s* d, pb2_gpu_task_t* t) {
     pb2_copy_t* fresh[PB2_MAX_PARAM_COUNT] = {nullptr};
     for (int i = 0; i < t->nb_flows; ++i) {
@@ -339,49 +381,15 @@ static int reserve_device_space(pb2_device_s* d, pb2_gpu_task_t* t) {
             }
             continue;
         }
-        void* mem = nullptr;
-        while (!(mem = d->heap->alloc(t->flow_nb_elts[i]))) {
-            // evict from the clean LRU (:934-1113)
-            pb2_copy_t* victim = nullptr;
-            std::vector<pb2_copy_t*> skipped;
-            while (pb2_copy_t* cand = d->lru.pop_front()) {
-                if (cand->readers != 0) continue;  // dropped from the list; pop re-files it when readers hit 0
-                bool mine = false;
-                for (int j = 0; j < t->nb_flows; ++j)
-                    if (t->flow_data[j] && cand->original == t->flow_data[j]) mine = true;
-                if (mine) {  // one of this task's own tiles: never steal it, look further (:1041-1062)
-                    skipped.push_back(cand);
-                    continue;
+        void* mem = alloc_evicting(d, t->flow_nb_elts[i], t);
+        if (!mem) {
+            // no room: keep what we created reachable at the LRU head and give up for now (:940-966)
+            for (int j = 0; j < i; ++j)
+                if (fresh[j]) {
+                    CopyList::chop(fresh[j], d->lists);
+                    d->lru.push_front(fresh[j]);
                 }
-                victim = cand;
-                break;
-            }
-            for (auto it = skipped.rbegin(); it != skipped.rend(); ++it) d->lru.push_front(*it);
-            if (!victim) {
-                // no room: keep what we created reachable at the LRU head and give up for now (:940-966)
-                for (int j = 0; j < i; ++j)
-                    if (fresh[j]) {
-                        CopyList::chop(fresh[j], d->lists);
-                        d->lru.push_front(fresh[j]);
-                    }
-                return 1;
-            }
-            if (d->params.trace_events && victim->original) {
-                pb2_event_t e;
-                memset(&e, 0, sizeof(e));
-                e.dc = victim->original->dc_id;
-                e.key = (uint32_t)victim->original->key;
-                e.kind = EV_EVICT;
-                e.k = -1;
-                e.gpu_version = victim->version;
-                e.cpu_version = victim->original->host_copy.version;
-                e.gpu_coh = victim->coherency_state;
-                e.cpu_coh = victim->original->host_copy.coherency_state;
-                e.owner_device = victim->original->owner_device;
-                d->events.push_back(e);
-            }
-            release_copy(d, victim);
-            d->stats.nb_evictions++;
+            return 1;
         }
         c = new pb2_copy_t();
         c->flags = PB2_FLAG_OWNED | PB2_FLAG_MANAGED;
@@ -836,3 +844,94 @@ extern "C" int pb2_zone_free(void* z, int64_t offset) {
     return h->free(h->base() + offset) ? PB2_SUCCESS : PB2_ERR_NOT_FOUND;
 }
 extern "C" size_t pb2_zone_in_use(void* z) { return ((ZoneHeap*)z)->in_use(); }
+
+// ------------------------------------------------------------------------------------ hooks for the comm layer
+// Used by the broadcast data plane (comm_nccl.cu) from the thread that holds the manager seat (pb2_device_hold),
+// i.e. while no manager loop is touching the lists.  Not part of the public header.
+
+// Make sure `data` has a valid device copy (staging it from the host through the normal reserve / stage-in path if it
+// has none), register one more reader so that it cannot be evicted, and make `wait_stream` wait until its bytes
+// are valid.  This is what a READ flow of a task does, minus the task.
+extern "C" int pb2_device_pin_for_read(pb2_device_t* d, pb2_data_t* data, void** dev_ptr, void* wait_stream) {
+    if (!d || !data || !dev_ptr) return PB2_ERR_BAD_PARAM;
+    cudaSetDevice(d->cuda_index);
+    pb2_gpu_task_t t;
+    memset(&t, 0, sizeof(t));
+    t.task_type = 1;
+    t.nb_flows = 1;
+    t.flow_data[0] = data;
+    t.flow_access[0] = PB2_FLOW_ACCESS_READ;
+    t.flow_nb_elts[0] = data->nb_elts;
+    t.trace_dc[0] = (int32_t)data->dc_id;
+    t.locals[2] = -1;
+    if (reserve_device_space(d, &t) != 0) return PB2_ERR_OUT_OF_RESOURCE;
+    TaskState st;
+    bool issued = false;
+    if (stage_in_flow(d, &t, &st, 0, &issued) < 0) return PB2_ERROR;
+    if (issued) {
+        d->h2d_seq++;
+        cudaEventRecord(d->h2d_events[d->h2d_seq % EVENT_RING], d->h2d);
+        complete_push_flow(d, &t, 0);
+    }
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (wait_stream && c->ready_seq) {
+        uint64_t w = (d->h2d_seq - c->ready_seq >= (uint64_t)EVENT_RING) ? d->h2d_seq : c->ready_seq;
+        cudaStreamWaitEvent((cudaStream_t)wait_stream, d->h2d_events[w % EVENT_RING], 0);
+    }
+    if (wait_stream && c->ready_event) cudaStreamWaitEvent((cudaStream_t)wait_stream, c->ready_event, 0);
+    *dev_ptr = c->device_private;
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_device_unpin(pb2_device_t* d, pb2_data_t* data) {
+    if (!d || !data) return PB2_ERR_BAD_PARAM;
+    std::lock_guard<std::mutex> g(data->lock);
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (!c) return PB2_ERR_NOT_FOUND;
+    c->readers--;
+    if (c->readers == 0 && c->list_id == 0 && c->coherency_state != PB2_DATA_COHERENCY_OWNED) d->lru.push_back(c);
+    return PB2_SUCCESS;
+}
+
+// A tile that arrives from a peer GPU: give it an HBM slot and a device copy that is already SHARED with the
+// sender's version, so that the consumer's stage-in finds "on the device, right version" and issues no H2D.  The
+// copy is in no LRU list (it has no host backing to fall back on) until pb2_device_drop_remote.
+extern "C" int pb2_device_adopt_remote(pb2_device_t* d, pb2_data_t* data, uint32_t version, void** dev_ptr) {
+    if (!d || !data || !dev_ptr) return PB2_ERR_BAD_PARAM;
+    if (data->device_copies[d->device_index]) return PB2_ERR_EXISTS;
+    void* mem = alloc_evicting(d, data->nb_elts, nullptr);
+    if (!mem) return PB2_ERR_OUT_OF_RESOURCE;
+    pb2_copy_t* c = new pb2_copy_t();
+    c->flags = PB2_FLAG_OWNED | PB2_FLAG_MANAGED;
+    c->device_private = mem;
+    c->coherency_state = PB2_DATA_COHERENCY_SHARED;
+    c->data_transfer_status = PB2_XFER_COMPLETE;
+    c->version = version;
+    c->readers = 1;  // held until pb2_device_drop_remote: there is no host copy to re-stage it from
+    c->device_index = (int8_t)d->device_index;
+    c->original = data;
+    data->device_copies[d->device_index] = c;
+    data->host_copy.version = version;
+    data->host_copy.coherency_state = PB2_DATA_COHERENCY_SHARED;
+    d->stats.data_in_from_peers += data->nb_elts;
+    *dev_ptr = mem;
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_device_set_ready_event(pb2_device_t* d, pb2_data_t* data, void* cuda_event) {
+    if (!d || !data) return PB2_ERR_BAD_PARAM;
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (!c) return PB2_ERR_NOT_FOUND;
+    c->ready_event = (cudaEvent_t)cuda_event;
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data) {
+    if (!d || !data) return PB2_ERR_BAD_PARAM;
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (!c) return PB2_ERR_NOT_FOUND;
+    release_copy(d, c);
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_device_exec_streams(pb2_device_t* d) { return d ? (int)d->exec.size() : 0; }

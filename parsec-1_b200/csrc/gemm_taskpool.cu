@@ -9,9 +9,10 @@
 //                                                 -> (k==KT-1) ? descC : C GEMM(m,n,k+1)
 //                 BODY [type=CUDA dyld=parsec_b200_dgemm]
 //
-// Owner-computes: a rank runs the chains of the C tiles it owns.  The C-ABI keeps the reference's split
-// between "the hook builds a parsec_gpu_task_t" and "the device module runs it": this file only builds tasks
-// and reacts to completions, exactly like the generated code.
+// Owner-computes: a rank runs the chains of the C tiles it owns (task affinity descC(m,n)); READ_A / READ_B run
+// where their tile lives and their ranged output deps are what becomes the row / column broadcasts
+// (comm_nccl.cu).  The C ABI keeps the reference's split between "the hook builds a parsec_gpu_task_t" and
+// "the device module runs it": this file only builds tasks and reacts to completions, like the generated code.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -21,11 +22,16 @@
 #include "pb2_internal.h"
 #include "pb2_types.h"
 
-extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out);
-extern "C" int pb2_device_hold(pb2_device_t* dev);
-extern "C" int pb2_device_manage(pb2_device_t* dev);
-extern "C" int parsec_b200_gemm_bf16_sm100(char, char, int, int, int, float, const void*, int, const void*, int, float,
-                                           float*, int, void*);
+extern "C" {
+int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out);
+void* pb2_comm_stream(pb2_comm_t* c);
+int pb2_comm_geometry(const pb2_comm_t* c, int* out);
+int pb2_device_pin_for_read(pb2_device_t* d, pb2_data_t* data, void** dev_ptr, void* wait_stream);
+int pb2_device_unpin(pb2_device_t* d, pb2_data_t* data);
+int pb2_device_adopt_remote(pb2_device_t* d, pb2_data_t* data, uint32_t version, void** dev_ptr);
+int pb2_device_set_ready_event(pb2_device_t* d, pb2_data_t* data, void* cuda_event);
+int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data);
+}
 
 struct Geo {
     int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id;
@@ -39,15 +45,22 @@ static Geo geo_of(const pb2_matrix_block_cyclic_t* dc) {
 struct pb2_taskpool_s {
     pb2_matrix_block_cyclic_t *A, *B, *C;
     pb2_device_t* dev;
+    pb2_comm_t* comm = nullptr;
     Geo gA, gB, gC;
-    int MT, NT, KT;
+    int MT, NT, KT, P, Q, myrow, mycol;
     int64_t window = 0;  // chains in flight (0 = all)
-    int64_t panel_cols = 0;
     std::vector<std::pair<int, int>> chains;
     size_t next_chain = 0;
     int64_t nb_gemm = 0, nb_read_a = 0, nb_read_b = 0;
     int status = 0;
+    // tiles of A / B this rank's GEMMs read: local rows x KT and KT x local columns; remote ones are proxies
+    std::vector<pb2_data_s*> a_tiles, b_tiles;
+    std::vector<pb2_data_s*> proxies, pinned;
+    std::vector<cudaEvent_t> comm_events;
 };
+
+static pb2_data_s* a_tile(pb2_taskpool_s* tp, int m, int k) { return tp->a_tiles[(size_t)(m / tp->P) * tp->KT + k]; }
+static pb2_data_s* b_tile(pb2_taskpool_s* tp, int k, int n) { return tp->b_tiles[(size_t)(n / tp->Q) * tp->KT + k]; }
 
 static int gemm_submit(pb2_device_t* dev, pb2_gpu_task_t* t, void* stream) {
     (void)dev;
@@ -73,8 +86,8 @@ static int spawn_gemm(pb2_taskpool_s* tp, int m, int n, int k) {
     t->task_type = 0;
     t->submit = gemm_submit;
     t->nb_flows = 3;
-    t->flow_data[0] = pb2_matrix_data_of(tp->A, m, k);
-    t->flow_data[1] = pb2_matrix_data_of(tp->B, k, n);
+    t->flow_data[0] = a_tile(tp, m, k);
+    t->flow_data[1] = b_tile(tp, k, n);
     t->flow_data[2] = pb2_matrix_data_of(tp->C, m, n);
     if (!t->flow_data[0] || !t->flow_data[1] || !t->flow_data[2]) {
         free(t);
@@ -138,7 +151,8 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
     // C (M x N) += A (M x K) * B (K x N): conforming tilings on one process grid
     bool ok = tp->gA.m == tp->gC.m && tp->gB.n == tp->gC.n && tp->gA.n == tp->gB.m && tp->gA.mb == tp->gC.mb &&
               tp->gB.nb == tp->gC.nb && tp->gA.nb == tp->gB.mb && tp->gA.P == tp->gC.P && tp->gA.Q == tp->gC.Q &&
-              tp->gB.P == tp->gC.P && tp->gB.Q == tp->gC.Q && tp->gA.mtype == tp->gB.mtype;
+              tp->gB.P == tp->gC.P && tp->gB.Q == tp->gC.Q && tp->gA.mtype == tp->gB.mtype &&
+              tp->gA.rank == tp->gC.rank && tp->gB.rank == tp->gC.rank;
     bool types = (tp->gC.mtype == PB2_MATRIX_DOUBLE && tp->gA.mtype == PB2_MATRIX_DOUBLE) ||
                  (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16);
     if (!ok || !types) {
@@ -146,48 +160,146 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
         return nullptr;
     }
     tp->MT = tp->gC.mt; tp->NT = tp->gC.nt; tp->KT = tp->gA.nt;
+    tp->P = tp->gC.P; tp->Q = tp->gC.Q;
+    tp->myrow = tp->gC.rank / tp->Q;
+    tp->mycol = tp->gC.rank % tp->Q;
     return tp;
 }
 
 extern "C" int pb2_gemm_taskpool_set(pb2_taskpool_t* tp, const char* key, int64_t value) {
     if (!tp || !key) return PB2_ERR_BAD_PARAM;
     if (!strcmp(key, "window")) tp->window = value;
-    else if (!strcmp(key, "panel_cols")) tp->panel_cols = value;
     else return PB2_ERR_NOT_FOUND;
+    return PB2_SUCCESS;
+}
+
+// The communicator a P x Q taskpool moves its A / B tiles with (pb2_comm_create); must match the descriptors' grid.
+extern "C" int pb2_gemm_taskpool_set_comm(pb2_taskpool_t* tp, pb2_comm_t* comm) {
+    if (!tp) return PB2_ERR_BAD_PARAM;
+    if (comm) {
+        int g[5];
+        pb2_comm_geometry(comm, g);
+        if (g[0] != tp->P || g[1] != tp->Q || g[2] != tp->gC.rank) return PB2_ERR_BAD_PARAM;
+    }
+    tp->comm = comm;
     return PB2_SUCCESS;
 }
 
 extern "C" void pb2_gemm_taskpool_free(pb2_taskpool_t* tp) { delete tp; }
 
+// Collect the A / B tiles this rank's GEMMs read and, on a P x Q grid, move the remote ones: the whole broadcast
+// schedule is enqueued up front on the comm stream in canonical order; consumers wait on per-step events.
+static int prepare_operands(pb2_taskpool_s* tp) {
+    const int rows = (tp->MT - tp->myrow + tp->P - 1) / tp->P, cols = (tp->NT - tp->mycol + tp->Q - 1) / tp->Q;
+    tp->a_tiles.assign((size_t)std::max(rows, 0) * tp->KT, nullptr);
+    tp->b_tiles.assign((size_t)std::max(cols, 0) * tp->KT, nullptr);
+    const uint32_t a_bytes = (uint32_t)((size_t)tp->gA.mb * tp->gA.nb * tp->gA.es);
+    const uint32_t b_bytes = (uint32_t)((size_t)tp->gB.mb * tp->gB.nb * tp->gB.es);
+    for (int m = tp->myrow; m < tp->MT; m += tp->P)
+        for (int k = 0; k < tp->KT; ++k) {
+            pb2_data_s* d = pb2_matrix_data_of(tp->A, m, k);
+            if (d) tp->nb_read_a++;  // READ_A(m,k) runs here
+            else {
+                d = pb2_data_create(pb2_matrix_data_key(tp->A, m, k), (uint32_t)tp->gA.dc_id, nullptr, a_bytes);
+                tp->proxies.push_back(d);
+            }
+            tp->a_tiles[(size_t)(m / tp->P) * tp->KT + k] = d;
+        }
+    for (int n = tp->mycol; n < tp->NT; n += tp->Q)
+        for (int k = 0; k < tp->KT; ++k) {
+            pb2_data_s* d = pb2_matrix_data_of(tp->B, k, n);
+            if (d) tp->nb_read_b++;
+            else {
+                d = pb2_data_create(pb2_matrix_data_key(tp->B, k, n), (uint32_t)tp->gB.dc_id, nullptr, b_bytes);
+                tp->proxies.push_back(d);
+            }
+            tp->b_tiles[(size_t)(n / tp->Q) * tp->KT + k] = d;
+        }
+    if (tp->P * tp->Q == 1) return PB2_SUCCESS;
+    // READ tasks of tiles that only feed remote GEMMs still execute on their owner: count the owned tiles outside the
+    // rows / columns walked above (none on a grid where every rank owns C tiles in each of its rows and columns).
+    int64_t nops = pb2_comm_plan(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, nullptr, 0);
+    std::vector<pb2_bcast_op_t> plan((size_t)nops);
+    pb2_comm_plan(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, plan.data(), nops);
+    cudaStream_t cs = (cudaStream_t)pb2_comm_stream(tp->comm);
+    std::vector<pb2_data_s*> group;  // received tiles waiting for their group's event
+    auto close_group = [&]() {
+        if (group.empty()) return;
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        cudaEventRecord(e, cs);
+        tp->comm_events.push_back(e);
+        for (pb2_data_s* d : group) pb2_device_set_ready_event(tp->dev, d, e);
+        group.clear();
+    };
+    int cur_k = -1, cur_which = -1;
+    for (const pb2_bcast_op_t& op : plan) {
+        if (op.k != cur_k || op.which != cur_which) {
+            close_group();
+            cur_k = op.k;
+            cur_which = op.which;
+        }
+        pb2_data_s* d = op.which == 0 ? a_tile(tp, op.idx, op.k) : b_tile(tp, op.k, op.idx);
+        void* ptr = nullptr;
+        int rc;
+        if (op.i_am_root) {
+            rc = pb2_device_pin_for_read(tp->dev, d, &ptr, cs);  // H2D if needed; the comm stream waits for it
+            if (rc == PB2_SUCCESS) tp->pinned.push_back(d);
+        } else {
+            rc = pb2_device_adopt_remote(tp->dev, d, 0, &ptr);   // sender's version: read-only operands are at 0
+            if (rc == PB2_SUCCESS) group.push_back(d);
+        }
+        if (rc != PB2_SUCCESS) {
+            fprintf(stderr, "[parsec_b200] cannot place tile (%s, k=%d, idx=%d) in HBM: %d\n", op.which ? "B" : "A", op.k,
+                    op.idx, rc);
+            return rc;
+        }
+        rc = pb2_comm_bcast(tp->comm, op.which, ptr, d->nb_elts, op.root);
+        if (rc != PB2_SUCCESS) return rc;
+    }
+    close_group();
+    return PB2_SUCCESS;
+}
+
+static void release_operands(pb2_taskpool_s* tp) {
+    if (tp->comm) cudaStreamSynchronize((cudaStream_t)pb2_comm_stream(tp->comm));
+    for (pb2_data_s* d : tp->pinned) pb2_device_unpin(tp->dev, d);
+    for (pb2_data_s* d : tp->proxies) pb2_data_destroy(d);  // frees the HBM slot of received tiles
+    for (cudaEvent_t e : tp->comm_events) cudaEventDestroy(e);
+    tp->pinned.clear();
+    tp->proxies.clear();
+    tp->comm_events.clear();
+    tp->a_tiles.clear();
+    tp->b_tiles.clear();
+}
+
 extern "C" int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats) {
     if (!tp) return PB2_ERR_BAD_PARAM;
-    if (tp->gC.P * tp->gC.Q != 1) {
-        fprintf(stderr, "[parsec_b200] multi-rank taskpools run through pb2_gemm_taskpool_run_dist (comm_nccl.cu)\n");
-        return PB2_ERR_NOT_SUPPORTED;
+    if (tp->P * tp->Q != 1 && !tp->comm) {
+        fprintf(stderr, "[parsec_b200] a %d x %d taskpool needs a communicator (pb2_gemm_taskpool_set_comm)\n", tp->P, tp->Q);
+        return PB2_ERR_BAD_PARAM;
     }
     auto t0 = std::chrono::steady_clock::now();
     tp->nb_gemm = tp->nb_read_a = tp->nb_read_b = 0;
     tp->status = 0;
     tp->chains.clear();
     tp->next_chain = 0;
-    // startup tasks: READ_A / READ_B have empty bodies and only forward the collection's tile
-    tp->nb_read_a = (int64_t)tp->MT * tp->KT;
-    tp->nb_read_b = (int64_t)tp->KT * tp->NT;
-    // chain activation order: column panels of C so that finished tiles leave while later panels compute
+    // chain activation order: column by column of C, so that finished tiles leave while later columns compute
     for (int n = 0; n < tp->NT; ++n)
-        for (int m = 0; m < tp->MT; ++m) tp->chains.push_back({m, n});
-    int64_t w = tp->window > 0 ? tp->window : (int64_t)tp->chains.size();
+        for (int m = 0; m < tp->MT; ++m)
+            if (pb2_matrix_rank_of(tp->C, m, n) == tp->gC.rank) tp->chains.push_back({m, n});
     if (!pb2_device_hold(tp->dev)) return PB2_ERROR;  // somebody else is driving this device
-    while (tp->next_chain < tp->chains.size() && (int64_t)tp->next_chain < w) {
+    int rc = prepare_operands(tp);
+    if (rc != PB2_SUCCESS) tp->status = rc;
+    int64_t w = tp->window > 0 ? tp->window : (int64_t)tp->chains.size();
+    while (!tp->status && tp->next_chain < tp->chains.size() && (int64_t)tp->next_chain < w) {
         auto mn = tp->chains[tp->next_chain++];
-        int rc = spawn_gemm(tp, mn.first, mn.second, 0);
-        if (rc) {
-            tp->status = rc;
-            break;
-        }
+        rc = spawn_gemm(tp, mn.first, mn.second, 0);
+        if (rc) tp->status = rc;
     }
-    int rc = pb2_device_manage(tp->dev);  // add_taskpool + start + wait
+    rc = pb2_device_manage(tp->dev);  // add_taskpool + start + wait
     if (rc != PB2_SUCCESS && !tp->status) tp->status = rc;
+    release_operands(tp);
     auto t1 = std::chrono::steady_clock::now();
     if (stats) {
         stats->nb_gemm = tp->nb_gemm;

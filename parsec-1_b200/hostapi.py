@@ -207,12 +207,78 @@ class Matrix:
             self.h = None
 
 
-def tiled_gemm(A, B, Cm, dev, **knobs):
+class BcastOp(C.Structure):
+    _fields_ = [("which", C.c_int32), ("k", C.c_int32), ("idx", C.c_int32), ("root", C.c_int32),
+                ("i_am_root", C.c_int32)]
+
+
+def comm_plan(P, Q, rank, MT, NT, KT):
+    """pb2_comm_plan: this rank's canonical broadcast sequence as a list of (which, k, idx, root, i_am_root)."""
+    L = lib()
+    L.pb2_comm_plan.restype = C.c_int64
+    L.pb2_comm_plan.argtypes = [C.c_int] * 6 + [C.c_void_p, C.c_int64]
+    n = L.pb2_comm_plan(P, Q, rank, MT, NT, KT, None, 0)
+    if n < 0:
+        raise ValueError("pb2_comm_plan rejected the arguments (%d)" % n)
+    ops = (BcastOp * max(n, 1))()
+    L.pb2_comm_plan(P, Q, rank, MT, NT, KT, ops, n)
+    return [(o.which, o.k, o.idx, o.root, o.i_am_root) for o in ops[:n]]
+
+
+def grid_for(world):
+    """P x Q with P <= Q, as square as possible: 1 -> 1x1, 2 -> 1x2, 4 -> 2x2, 8 -> 2x4."""
+    p = int(world ** 0.5)
+    while world % p:
+        p -= 1
+    return p, world // p
+
+
+class Comm:
+    """pb2_comm_t: row / column NCCL communicators of a P x Q grid; ids are exchanged over torch.distributed."""
+
+    def __init__(self, cuda_index, P, Q, rank):
+        import torch
+        import torch.distributed as dist
+        L = lib()
+        L.pb2_comm_unique_id.argtypes = [C.c_void_p]
+        L.pb2_comm_create.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pb2_comm_destroy.argtypes = [C.c_void_p]
+        L.pb2_gemm_taskpool_set_comm.argtypes = [C.c_void_p, C.c_void_p]
+        # every rank publishes two ids; the row communicator of process row r uses the first id of rank (r, 0), the
+        # column communicator of process column c the second id of rank (0, c)
+        ids = (C.c_ubyte * 256)()
+        for off in (0, 128):
+            if L.pb2_comm_unique_id(C.byref(ids, off)) != SUCCESS:
+                raise RuntimeError("ncclGetUniqueId failed")
+        dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+        t = torch.tensor(list(ids), dtype=torch.uint8, device=dev)
+        allids = [torch.empty_like(t) for _ in range(P * Q)]
+        dist.all_gather(allids, t)
+        myrow, mycol = rank // Q, rank % Q
+        self._row = (C.c_ubyte * 128).from_buffer_copy(bytes(allids[myrow * Q].cpu().tolist()[:128]))
+        self._col = (C.c_ubyte * 128).from_buffer_copy(bytes(allids[mycol].cpu().tolist()[128:]))
+        h = C.c_void_p()
+        rc = L.pb2_comm_create(cuda_index, P, Q, rank, self._row, self._col, C.byref(h))
+        if rc != SUCCESS:
+            raise RuntimeError("pb2_comm_create failed (%d)" % rc)
+        self.h, self.P, self.Q, self.rank = h, P, Q, rank
+
+    def close(self):
+        if self.h:
+            lib().pb2_comm_destroy(self.h)
+            self.h = None
+
+
+def tiled_gemm(A, B, Cm, dev, comm=None, **knobs):
     """C += A * B through the device pipeline (parsec_dgemm_NN taskpool: add_taskpool + start + wait)."""
     tp = C.c_void_p(lib().pb2_gemm_taskpool_new(A.h, B.h, Cm.h, dev.h))
     if not tp:
         raise ValueError("pb2_gemm_taskpool_new rejected the descriptors (non-conforming tilings or dtypes)")
     try:
+        if comm is not None:
+            lib().pb2_gemm_taskpool_set_comm.argtypes = [C.c_void_p, C.c_void_p]
+            if lib().pb2_gemm_taskpool_set_comm(tp, comm.h) != SUCCESS:
+                raise ValueError("communicator does not match the descriptors' process grid")
         for k, v in knobs.items():
             if lib().pb2_gemm_taskpool_set(tp, k.encode(), int(v)) != SUCCESS:
                 raise KeyError(k)

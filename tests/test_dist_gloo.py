@@ -1,0 +1,142 @@
+"""Host-side logic of the P x Q data plane on the CPU: the broadcast plan (pb2_comm_plan, through the C ABI) is
+checked for consistency across ranks, and then executed by two gloo processes with torch.distributed.broadcast
+standing in for ncclBroadcast; the tile arithmetic is the oracle's.  No GPU involved."""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import load_hostapi
+
+H = load_hostapi()
+
+
+@pytest.mark.parametrize("P,Q,MT,NT,KT", [(1, 2, 4, 4, 4), (2, 2, 5, 3, 4), (2, 4, 8, 8, 8), (3, 2, 7, 5, 3), (1, 1, 3, 3, 3)])
+def test_plan_is_consistent_across_ranks(P, Q, MT, NT, KT):
+    plans = {r: H.comm_plan(P, Q, r, MT, NT, KT) for r in range(P * Q)}
+    dA = O.bc(0, 1, 1, MT, KT, 0, 0, MT, KT, P, Q)
+    dB = O.bc(0, 1, 1, KT, NT, 0, 0, KT, NT, P, Q)
+    if P * Q == 1:
+        assert plans[0] == []
+        return
+    # every member of a communicator issues the same sequence on it, exactly one member roots each op, and the root
+    # is the tile's owner under twoDBC_rank_of
+    for row in range(P):
+        members = [row * Q + c for c in range(Q)]
+        seqs = [[op[:4] for op in plans[r] if op[0] == 0] for r in members]
+        assert all(s == seqs[0] for s in seqs)
+        if Q > 1:
+            assert sorted((k, m) for (_, k, m, _) in seqs[0]) == [(k, m) for k in range(KT) for m in range(row, MT, P)]
+        for i, (_, k, m, root) in enumerate(seqs[0]):
+            roots = [r for r in members if [op for op in plans[r] if op[0] == 0][i][4]]
+            assert roots == [row * Q + root] == [O.lib().orc_bc_rank_of(C.byref(dA), m, k)]
+    for col in range(Q):
+        members = [r * Q + col for r in range(P)]
+        seqs = [[op[:4] for op in plans[r] if op[0] == 1] for r in members]
+        assert all(s == seqs[0] for s in seqs)
+        if P > 1:
+            assert sorted((k, n) for (_, k, n, _) in seqs[0]) == [(k, n) for k in range(KT) for n in range(col, NT, Q)]
+        for i, (_, k, n, root) in enumerate(seqs[0]):
+            roots = [r for r in members if [op for op in plans[r] if op[0] == 1][i][4]]
+            assert roots == [root * Q + col] == [O.lib().orc_bc_rank_of(C.byref(dB), k, n)]
+    # canonical order inside a rank: k ascending, rows before columns inside a step
+    for r, ops in plans.items():
+        assert [(k, which) for (which, k, _, _, _) in ops] == sorted((k, which) for (which, k, _, _, _) in ops)
+
+
+def test_plan_rejects_bad_arguments():
+    with pytest.raises(ValueError):
+        H.comm_plan(2, 2, 4, 4, 4, 4)
+    with pytest.raises(ValueError):
+        H.comm_plan(0, 2, 0, 4, 4, 4)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, P, Q, N, NB, out_dir):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        MT = N // NB
+        descs = [O.square(N, NB, P, Q, rank) for _ in range(3)]
+        local = [O.fill(d, s) for d, s in zip(descs, (1789, 1805, 1901))]
+        myrow, mycol = rank // Q, rank % Q
+        row_group = dist.new_group([myrow * Q + c for c in range(Q)]) if Q > 1 else None
+        for r in range(P):  # new_group is collective over the world: every rank creates every group
+            if r != myrow and Q > 1:
+                dist.new_group([r * Q + c for c in range(Q)])
+        col_groups = {}
+        for c in range(Q):
+            if P > 1:
+                g = dist.new_group([r * Q + c for r in range(P)])
+                if c == mycol:
+                    col_groups[c] = g
+
+        def tile_of(which, a, b):
+            d, mat = (descs[0], local[0]) if which == 0 else (descs[1], local[1])
+            pos = O.lib().orc_bc_position(C.byref(d), a, b)
+            return mat[pos * NB * NB:(pos + 1) * NB * NB]
+
+        got = {}
+        for (which, k, idx, root, i_am_root) in H.comm_plan(P, Q, rank, MT, MT, MT):
+            buf = torch.from_numpy(tile_of(which, idx, k).copy() if which == 0 and i_am_root else
+                                   tile_of(which, k, idx).copy() if i_am_root else np.zeros(NB * NB))
+            if which == 0:
+                dist.broadcast(buf, src=myrow * Q + root, group=row_group)
+            else:
+                dist.broadcast(buf, src=root * Q + mycol, group=col_groups[mycol])
+            got[(which, k, idx)] = buf.numpy()
+
+        def operand(which, a, b):  # A(a, b) or B(a, b)
+            key = (0, b, a) if which == 0 else (1, a, b)
+            if key in got:
+                return got[key]
+            return tile_of(which, a, b)
+
+        result = {}
+        for n in range(MT):
+            for m in range(MT):
+                if O.lib().orc_bc_rank_of(C.byref(descs[2]), m, n) != rank:
+                    continue
+                pos = O.lib().orc_bc_position(C.byref(descs[2]), m, n)
+                c = local[2][pos * NB * NB:(pos + 1) * NB * NB].reshape((NB, NB), order="F").copy(order="F")
+                for k in range(MT):
+                    a = operand(0, m, k).reshape((NB, NB), order="F")
+                    b = operand(1, k, n).reshape((NB, NB), order="F")
+                    O.dgemm_tile(1.0, np.asfortranarray(a), np.asfortranarray(b), 1.0, c)
+                result[(m, n)] = c
+        np.save(os.path.join(out_dir, "rank%d.npy" % rank), result, allow_pickle=True)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1)])
+def test_two_gloo_ranks_reproduce_the_single_rank_result(tmp_path, P, Q):
+    import torch.multiprocessing as mp
+    N, NB = 256, 64
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, P, Q, N, NB, str(tmp_path)), nprocs=2, join=True)
+    d = O.square(N, NB)
+    A, B, Cm = O.fill(d, 1789), O.fill(d, 1805), O.fill(d, 1901)
+    O.tiled_dgemm(N, N, N, NB, NB, NB, A, B, Cm)
+    seen = 0
+    for rank in range(2):
+        res = np.load(os.path.join(str(tmp_path), "rank%d.npy" % rank), allow_pickle=True).item()
+        for (m, n), tile in res.items():
+            pos = O.lib().orc_bc_position(C.byref(d), m, n)
+            want = Cm[pos * NB * NB:(pos + 1) * NB * NB].reshape((NB, NB), order="F")
+            assert np.array_equal(tile, want)  # same tile arithmetic in the same k order: bit-identical
+            seen += 1
+    assert seen == (N // NB) ** 2
