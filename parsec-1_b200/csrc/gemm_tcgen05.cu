@@ -1,9 +1,273 @@
-// BF16-in / FP32-accumulate tile GEMM (tcgen05 + TMEM + TMA).  Placeholder until the kernel lands.
+// BF16-in / FP32-accumulate tile GEMM on the 5th-generation tensor cores: tcgen05.mma with the accumulator in
+// TMEM, operands staged by TMA (128-byte swizzle), warp-specialised roles, mbarrier pipelines.
+//
+//   C (m x n, fp32, column-major) = alpha * A (m x k, bf16, column-major) * B (k x n, bf16, column-major) + beta * C
+//
+// This is the BASELINE config 5 body (NB = 2048 tiles): the reference has no bf16 body at all (its
+// parsec_matrix_type_t has no 16-bit float, matrix.h:25-32); the call shape follows its cublasDgemm_v2 bodies.
+//
+// Operand orientation, no transposes anywhere:
+//   A is column-major, i.e. M is contiguous  -> UMMA "MN-major" operand.  One stage holds two TMA boxes
+//        [64 k][64 m] (128-byte rows of 64 bf16 along m): exactly the canonical SW128 MN-major layout
+//        ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units, LBO = 8 KiB (next 64 rows of m), SBO = 1 KiB (next 8 k).
+//   B is column-major k x n, i.e. K is contiguous -> UMMA "K-major" operand.  One TMA box [256 n][64 k]
+//        (128-byte rows of 64 bf16 along k): canonical SW128 K-major layout, SBO = 1 KiB (next 8 rows of n).
+//   D lives in TMEM: 128 lanes (rows of the tile) x 256 fp32 columns.  The epilogue reads 32 columns per
+//        tcgen05.ld (one row per thread), so for a fixed column a warp holds 32 consecutive rows: column-major
+//        stores to C are 128-byte coalesced.
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2-5 = epilogue (warp w may only touch TMEM lanes 32*(w%4) .. +31, and 2,3,4,5 cover all four quarters).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
 #include "pb2_internal.h"
+#include "tma_utils.cuh"
+
+namespace pb2 {
+
+constexpr int G_BM = 128, G_BN = 256, G_BK = 64;
+constexpr int G_STAGES = 4;
+constexpr int G_A_BYTES = G_BM * G_BK * 2;  // 16 KiB: two [64 k][64 m] boxes
+constexpr int G_B_BYTES = G_BN * G_BK * 2;  // 32 KiB: one [256 n][64 k] box
+constexpr int G_STAGE_BYTES = G_A_BYTES + G_B_BYTES;
+constexpr int G_THREADS = 192;
+constexpr int G_TMEM_COLS = 256;
+constexpr size_t G_SMEM = (size_t)G_STAGES * G_STAGE_BYTES + 1024 + 256;
+
+// instruction descriptor, kind::f16 (cute/arch/mma_sm100_desc.hpp InstrDescriptor):
+//   [4,6) c_format = 1 (F32); [7,10) a_format = 1 (BF16); [10,13) b_format = 1 (BF16);
+//   [15] a_major = 1 (MN-major); [16] b_major = 0 (K-major); [17,23) N >> 3; [24,29) M >> 4
+constexpr uint32_t G_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((uint32_t)(G_BN >> 3) << 17) |
+                             ((uint32_t)(G_BM >> 4) << 24);
+
+// shared-memory matrix descriptor (SmemDescriptor): [0,14) start >> 4; [16,30) LBO >> 4; [32,46) SBO >> 4;
+// [46,48) version = 1; [61,64) layout type = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(smem_dst)), "r"(ncols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols));
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives on the mbarrier once every MMA issued so far by this thread has completed (implies fence::before_thread_sync)
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// 32 lanes x 32 columns of 32-bit: thread t of the warp receives columns [c, c+32) of lane (base lane + t)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+
+__global__ void __launch_bounds__(G_THREADS, 1)
+gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
+                  float alpha, float beta, float* __restrict__ C, int ldc) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase0 = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (sbase0 - raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES);
+    uint64_t* empty = full + G_STAGES;
+    uint64_t* tmem_full = empty + G_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_m = (M + G_BM - 1) / G_BM;
+    const int m0 = (blockIdx.x % tiles_m) * G_BM, n0 = (blockIdx.x / tiles_m) * G_BN;
+    const int KT = (K + G_BK - 1) / G_BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < G_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, G_TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0 && KT > 0) {
+            tma_prefetch_desc(&mapA);
+            tma_prefetch_desc(&mapB);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = 0; kt < KT; ++kt) {
+                if (kt >= G_STAGES) mbar_wait(&empty[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * G_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full[stage], G_STAGE_BYTES);
+                tma_load_2d(sa, &mapA, m0, kt * G_BK, &full[stage]);
+                tma_load_2d(sa + G_A_BYTES / 2, &mapA, m0 + 64, kt * G_BK, &full[stage]);
+                tma_load_2d(sa + G_A_BYTES, &mapB, kt * G_BK, n0, &full[stage]);
+                if (++stage == G_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = 0; kt < KT; ++kt) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = sbase0 + stage * G_STAGE_BYTES;
+                const uint32_t sb = sa + G_A_BYTES;
+#pragma unroll
+                for (int k16 = 0; k16 < G_BK / 16; ++k16) {
+                    // A: 16 k-rows of 128 B further per step; B: 32 bytes further inside the 128-byte swizzle row
+                    const uint64_t adesc = umma_desc(sa + k16 * 2048, G_A_BYTES / 2, 1024);
+                    const uint64_t bdesc = umma_desc(sb + k16 * 32, 16, 1024);
+                    umma_bf16(tmem_base, adesc, bdesc, G_IDESC, (kt | k16) != 0);
+                }
+                umma_commit(&empty[stage]);  // the stage may be refilled once these MMAs have read it
+                if (++stage == G_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            umma_commit(tmem_full);  // accumulator complete
+        }
+    } else {
+        // epilogue: TMEM -> registers -> global (column-major, 128-byte coalesced per column)
+        const int quarter = warp & 3;
+        const int row = m0 + quarter * 32 + lane;
+        if (KT > 0) {
+            mbar_wait(tmem_full, 0);
+            tc_fence_after();
+        }
+#pragma unroll 1
+        for (int c0 = 0; c0 < G_BN; c0 += 32) {
+            if (n0 + c0 >= N) break;  // warp-uniform
+            uint32_t v[32];
+            if (KT > 0) {
+                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0u;
+            }
+            if (row < M) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = n0 + c0 + j;
+                    if (col < N) {
+                        float* p = C + (size_t)row + (size_t)col * ldc;
+                        float r = alpha * __uint_as_float(v[j]);
+                        if (beta != 0.0f) r += beta * *p;
+                        *p = r;
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, G_TMEM_COLS);
+    }
+}
+
+static bool g_gemm_attr_set[64] = {false};
+
+struct BfMapKey {
+    const void* p;
+    int d0, d1, ld, kind;
+};
+struct BfMapEntry {
+    BfMapKey k;
+    CUtensorMap m;
+    bool valid;
+};
+static int bf16_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int kind) {
+    static thread_local BfMapEntry cache[512];
+    uintptr_t h = ((uintptr_t)p >> 9) * 0x9E3779B97F4A7C15ull + (uintptr_t)(d0 * 31 + d1 * 17 + ld * 7 + kind);
+    BfMapEntry& e = cache[(h >> 20) & 511];
+    if (e.valid && e.k.p == p && e.k.d0 == d0 && e.k.d1 == d1 && e.k.ld == ld && e.k.kind == kind) {
+        *out = e.m;
+        return 0;
+    }
+    int rc = kind == 0 ? encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p, d0, d1, ld, 64, G_BK,
+                                        CU_TENSOR_MAP_SWIZZLE_128B)
+                       : encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p, d0, d1, ld, G_BK, G_BN,
+                                        CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) {
+        e.valid = false;
+        return rc;
+    }
+    e.k = {p, d0, d1, ld, kind};
+    e.valid = true;
+    *out = e.m;
+    return 0;
+}
+
+}  // namespace pb2
+
 extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A,
                                            int lda, const void* B, int ldb, float beta, float* C, int ldc,
                                            void* stream) {
-    (void)transa; (void)transb; (void)m; (void)n; (void)k; (void)alpha; (void)A; (void)lda; (void)B; (void)ldb;
-    (void)beta; (void)C; (void)ldc; (void)stream;
-    return PB2_ERR_NOT_IMPLEMENTED;
+    using namespace pb2;
+    if ((transa != 'N' && transa != 'n') || (transb != 'N' && transb != 'n')) return PB2_ERR_NOT_SUPPORTED;
+    if (m < 0 || n < 0 || k < 0 || lda < (m > 1 ? m : 1) || ldb < (k > 1 ? k : 1) || ldc < (m > 1 ? m : 1))
+        return PB2_ERR_BAD_PARAM;
+    if (m == 0 || n == 0) return PB2_SUCCESS;
+    // TMA: 16-byte aligned bases and row pitches
+    if ((((uintptr_t)A | (uintptr_t)B) & 15) || (lda & 7) || (ldb & 7) || (((uintptr_t)C) & 3)) return PB2_ERR_NOT_SUPPORTED;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return PB2_ERR_CUDA;
+    if (dev < 64 && !g_gemm_attr_set[dev]) {
+        if (cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM) != cudaSuccess)
+            return PB2_ERR_CUDA;
+        g_gemm_attr_set[dev] = true;
+    }
+    CUtensorMap ma, mb;
+    if (k > 0 && (bf16_tmap(&ma, A, m, k, lda, 0) || bf16_tmap(&mb, B, k, n, ldb, 1))) return PB2_ERR_CUDA;
+    if (k == 0) {  // nothing to stage: the kernel only scales C; the maps are never dereferenced
+        memset(&ma, 0, sizeof(ma));
+        memset(&mb, 0, sizeof(mb));
+    }
+    dim3 grid(((m + G_BM - 1) / G_BM) * ((n + G_BN - 1) / G_BN));
+    gemm_bf16_tcgen05<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
 }

@@ -1,0 +1,75 @@
+"""tcgen05 / TMEM tile GEMM (bf16 in, fp32 accumulate) through the C ABI against the oracle's bf16 tile GEMM."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import load_hostapi
+
+pytestmark = pytest.mark.gpu
+H = load_hostapi()
+EPS32 = 2.0 ** -24
+
+
+def _bf16_bits(x):
+    """float32 array -> bf16 bit patterns (round to nearest even), same rule as orc_f32_to_bf16_rn."""
+    u = x.astype(np.float32).view(np.uint32).astype(np.uint64)
+    u = u + 0x7FFF + ((u >> 16) & 1)
+    return (u >> 16).astype(np.uint16)
+
+
+def _run(m, n, k, alpha, beta, seed=0, ld_pad=0):
+    import torch
+    rng = np.random.default_rng(seed)
+    A = np.asfortranarray(_bf16_bits(rng.uniform(-0.5, 0.5, (m, k))))
+    B = np.asfortranarray(_bf16_bits(rng.uniform(-0.5, 0.5, (k, n))))
+    Cm = np.asfortranarray(rng.uniform(-0.5, 0.5, (m, n)).astype(np.float32))
+    lda, ldb, ldc = m + ld_pad, k + ld_pad, m + ld_pad
+
+    def to_dev(X, ld, dtype):
+        buf = np.zeros((X.shape[1], ld), dtype=dtype)
+        buf[:, :X.shape[0]] = X.T
+        return torch.from_numpy(buf.view(np.int16) if dtype == np.uint16 else buf).cuda()
+
+    dA, dB, dC = to_dev(A, lda, np.uint16), to_dev(B, ldb, np.uint16), to_dev(Cm, ldc, np.float32)
+    rc = H.lib().parsec_b200_gemm_bf16_sm100(b"N", b"N", m, n, k, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta,
+                                              dC.data_ptr(), ldc, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    got = dC.cpu().numpy()[:, :m].T
+    want = Cm.copy(order="F")
+    O.lib().orc_gemm_tile_bf16(m, n, k, alpha, A.ctypes.data, m, B.ctypes.data, k, beta, want.ctypes.data, m)
+    back = lambda X: (X.astype(np.uint32) << 16).view(np.float32).astype(np.float64)
+    inf = lambda X: np.abs(X).sum(axis=1).max()
+    denom = max(abs(alpha) * inf(back(A)) * inf(back(B)) * max(k, 1) * EPS32, 1e-30)
+    return inf(got.astype(np.float64) - want.astype(np.float64)) / denom
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 256, 64), (128, 256, 256), (256, 512, 128), (1024, 1024, 1024), (2048, 2048, 2048)])
+def test_aligned_tiles(m, n, k):
+    # tolerance: ||C - Cref||inf / (||A||inf ||B||inf K eps32) < 10 with eps32 = 2^-24 (fp32 accumulation)
+    assert _run(m, n, k, 1.0, 1.0, seed=m + k) < 10
+
+
+@pytest.mark.parametrize("m,n,k", [(64, 64, 64), (200, 136, 72), (136, 300, 16), (8, 8, 8), (1000, 520, 264)])
+def test_ragged_tiles(m, n, k):
+    assert _run(m, n, k, 1.0, 1.0, seed=n) < 10
+
+
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.0, 1.0), (-1.5, 0.5)])
+def test_alpha_beta(alpha, beta):
+    assert _run(256, 256, 256, alpha, beta, seed=9) < 10
+
+
+def test_padded_leading_dimension():
+    assert _run(256, 256, 128, 1.0, 1.0, seed=4, ld_pad=8) < 10
+
+
+def test_unsupported_arguments():
+    import torch
+    x = torch.zeros(4096, dtype=torch.float32, device="cuda")
+    p = x.data_ptr()
+    f = H.lib().parsec_b200_gemm_bf16_sm100
+    assert f(b"T", b"N", 8, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8, 0) == -7     # transposes: not supported
+    assert f(b"N", b"N", 8, 8, 8, 1.0, p, 4, p, 8, 1.0, p, 8, 0) == -4     # lda < m
+    assert f(b"N", b"N", 12, 8, 8, 1.0, p, 12, p, 8, 1.0, p, 12, 0) == -7  # lda not a multiple of 8 (TMA pitch)
+    assert f(b"N", b"N", 0, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8, 0) == 0
