@@ -144,6 +144,8 @@ def main():
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dtype", default="f64", choices=["f64", "bf16"],
+                    help="f64: the headline DGEMM; bf16: BF16-in/FP32-acc tiles on tcgen05 (BASELINE configs[4], use --nb 2048)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -167,11 +169,22 @@ def main():
     N = args.n if world == 1 else int(round(args.n * world ** (1.0 / 3.0) / NB)) * NB
     P, Q = H.grid_for(world)
     comm = H.Comm(local_rank, P, Q, rank) if world > 1 else None
-    peak_tf = fp64_peak_tflops(torch)
+    bf16 = args.dtype == "bf16"
+    mtypes = (H.MATRIX_BF16, H.MATRIX_BF16, H.MATRIX_FLOAT) if bf16 else (H.MATRIX_DOUBLE,) * 3
+    if bf16:
+        try:   # driver-written cuBLAS bf16 peaks; a kernel timed inside a seconds-long step compares to the sustained one
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak_tf, peak_src = float(peaks["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)"
+        except Exception:
+            peak_tf, peak_src = 1590.0, "B200_PROFILING.md fallback 1.59 PFLOP/s (of fallback)"
+    else:
+        peak_tf = fp64_peak_tflops(torch)
+        peak_src = ("measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10; MEASURED_PEAKS.json has no fp64 entry "
+                    "(DMMA issue peak measured 37.1 TFLOP/s, profiles/microbench_r1_v2_tma.log)")
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0)
     mats, bufs = [], []
-    for seed in (1789, 1805, 1901):
-        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank)
+    for seed, mtype in zip((1789, 1805, 1901), mtypes):
+        m = H.Matrix(mtype, N, N, NB, NB, P, Q, rank)
         b = torch.empty(max(m.nbytes, 8), dtype=torch.uint8, pin_memory=True)   # cudaHostAlloc: the collection's host memory
         m.set_buffer(b)
         m.fill_lcg(seed, dev)
@@ -231,8 +244,8 @@ def main():
     dev.close()
     dev = H.Device(local_rank, **dev2_params)
     mats = []
-    for b in bufs:
-        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank)
+    for b, mtype in zip(bufs, mtypes):
+        m = H.Matrix(mtype, N, N, NB, NB, P, Q, rank)
         m.set_buffer(b)
         mats.append(m)
     A, B, Cm = mats
@@ -254,14 +267,17 @@ def main():
     out = {
         "metric": "tiled GEMM GFLOP/s", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_resident, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": ("tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
+        "vs_baseline": None, "dtype": "bf16 in / f32 accumulate" if bf16 else "f64", "data": "synthetic",
+        "config": {"workload": ("mixed-precision tiled GEMM BF16-in/FP32-acc N=%d NB=%d via tcgen05 on %d B200 "
+                                "(BASELINE configs[4] shape)" % (N, NB, world)) if bf16 else
+                               ("tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
                                 "(BASELINE configs[1])" % (N, NB)) if world == 1 else
                                ("tiled DGEMM N=%d NB=%d fp64, 2D block-cyclic %dx%d over %d B200 with NCCL tile bcast "
                                 "(BASELINE configs[2] shape; weak scaling from N=%d)" % (N, NB, P, Q, world, args.n)),
-                   "tasks_per_step": (N // NB) ** 3, "l2": "inputs (3 x %.1f GiB) far larger than L2" % (N * N * 8 / 2 ** 30),
+                   "tasks_per_step": (N // NB) ** 3,
+                   "l2": "inputs (%.1f GiB) far larger than L2" % (N * N * (8 if bf16 else 24) / 2 ** 30),
                    "parallelism": "1 process per GPU, %dx%d grid; %d exec streams per GPU" % (P, Q, args.streams - 2),
-                   "pct_of_fp64_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
+                   "pct_of_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
         "e2e": {"value": e2e, "unit": "GFLOP/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": st_e2e["data_in_from_host"] // max(1, args.steps),
                 "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps),
@@ -269,12 +285,11 @@ def main():
         "gpu_launches": st_resident["kernel_launches"],
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": (achieved_tf / peak_tf) if prof else None, "traffic": 25206528,  # dram bytes per launch, ncu --set full (profiles/dgemm_tma_r1_ncu.md)
-                     
-                     "kernel": "pb2::dgemm_nn_tma", "peak_source": "measured live: torch.matmul fp64 8192^3 (cuBLAS), "
-                     "best of 10; MEASURED_PEAKS.json has no fp64 entry (DMMA issue peak measured 37.1 TFLOP/s, "
-                     "profiles/microbench_r1.md)", "detail": prof,
-                     "algorithmic_flops_per_launch": per_launch_flops},
+                     "frac": (achieved_tf / peak_tf) if prof else None,
+                     # dram bytes per launch from one ncu --set full capture (profiles/dgemm_tma_r1_ncu.md)
+                     "traffic": None if bf16 else 25206528,
+                     "kernel": "pb2::gemm_bf16_tcgen05" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
+                     "detail": prof, "algorithmic_flops_per_launch": per_launch_flops},
     }
     if rank == 0 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1

@@ -75,7 +75,10 @@ struct pb2_device_s {
     uint64_t h2d_seq = 0;  // number of push events recorded so far
     cudaEvent_t h2d_events[pb2::EVENT_RING];
     std::vector<cudaEvent_t> event_pool;
-    std::deque<pb2::InFlight> inflight;       // ordered by submission
+    // in flight, one FIFO per stream that carries the final event: exec streams, then d2h, then h2d (prefetches).
+    // Events of one stream complete in order, so only the heads are ever polled.
+    std::vector<std::deque<pb2::InFlight>> inflight_q;
+    size_t inflight_count = 0;
     std::deque<pb2_gpu_task_t*> stalled;      // tasks that found no room
     char* hbm_base = nullptr;
     pb2::ZoneHeap* heap = nullptr;
@@ -163,6 +166,7 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
     d->exec.resize(nexec);
     d->exec_waited_seq.assign(nexec, 0);
     d->launch_marks.resize(nexec);
+    d->inflight_q.resize(nexec + 2);
     for (int i = 0; i < nexec; ++i) PB2_CUDA_OK(cudaStreamCreateWithFlags(&d->exec[i], cudaStreamNonBlocking));
     for (int i = 0; i < EVENT_RING; ++i) PB2_CUDA_OK(cudaEventCreateWithFlags(&d->h2d_events[i], cudaEventDisableTiming));
 
@@ -483,7 +487,8 @@ static bool start_w2r(pb2_device_s* d) {
     }
     st->done = get_event(d);
     cudaEventRecord(st->done, d->d2h);
-    d->inflight.push_back({nullptr, st});
+    d->inflight_q[d->exec.size()].push_back({nullptr, st});
+    d->inflight_count++;
     d->stats.nb_w2r_tasks++;
     d->stats.nb_w2r_tiles += st->w2r_copies.size();
     return true;
@@ -588,7 +593,9 @@ static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
     } else {
         cudaEventRecord(st->done, last);
     }
-    d->inflight.push_back({t, st});
+    const size_t q = out_mask ? d->exec.size() : (st->exec_stream >= 0 ? (size_t)st->exec_stream : d->exec.size() + 1);
+    d->inflight_q[q].push_back({t, st});
+    d->inflight_count++;
     return 0;
 }
 
@@ -645,38 +652,35 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t) {
 
 static bool progress_completions(pb2_device_s* d) {
     bool any = false;
-    // completion order across streams is not submission order: scan a bounded window from the front
-    size_t scan = std::min<size_t>(d->inflight.size(), 64);
-    for (size_t idx = 0; idx < scan;) {
-        InFlight f = d->inflight[idx];
-        cudaError_t q = cudaEventQuery(f.st->done);
-        if (q == cudaErrorNotReady) {
-            ++idx;
-            continue;
-        }
-        if (q != cudaSuccess) {
-            fprintf(stderr, "[parsec_b200] device error while waiting for a task: %s\n", cudaGetErrorString(q));
-            d->failed = true;
-        }
-        d->inflight.erase(d->inflight.begin() + idx);
-        --scan;
-        d->event_pool.push_back(f.st->done);
-        any = true;
-        if (f.st->is_w2r) {
-            complete_w2r(d, f.st);
+    for (auto& queue : d->inflight_q) {
+        while (!queue.empty()) {
+            InFlight f = queue.front();
+            cudaError_t q = cudaEventQuery(f.st->done);
+            if (q == cudaErrorNotReady) break;
+            if (q != cudaSuccess) {
+                fprintf(stderr, "[parsec_b200] device error while waiting for a task: %s\n", cudaGetErrorString(q));
+                d->failed = true;
+            }
+            queue.pop_front();
+            d->inflight_count--;
+            d->event_pool.push_back(f.st->done);
+            any = true;
+            if (f.st->is_w2r) {
+                complete_w2r(d, f.st);
+                delete f.st;
+                continue;
+            }
+            pb2_gpu_task_t* t = f.task;
+            finish_task(d, t);
             delete f.st;
-            continue;
+            t->reserved[0] = nullptr;
+            if (t->complete) t->complete(t, d->failed ? PB2_HOOK_RETURN_ERROR : PB2_HOOK_RETURN_DONE, t->complete_cookie);
+            if (d->params.trace_events)
+                for (int i = 0; i < t->nb_flows; ++i)
+                    if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && t->flow_data[i]) trace(d, t, i, EV_COMPLETE, 0);
+            free(t);
+            d->mutex.fetch_sub(1);
         }
-        pb2_gpu_task_t* t = f.task;
-        finish_task(d, t);
-        delete f.st;
-        t->reserved[0] = nullptr;
-        if (t->complete) t->complete(t, d->failed ? PB2_HOOK_RETURN_ERROR : PB2_HOOK_RETURN_DONE, t->complete_cookie);
-        if (d->params.trace_events)
-            for (int i = 0; i < t->nb_flows; ++i)
-                if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && t->flow_data[i]) trace(d, t, i, EV_COMPLETE, 0);
-        free(t);
-        d->mutex.fetch_sub(1);
     }
     return any;
 }
@@ -724,14 +728,15 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
     pb2_gpu_task_t* cur = task;
     const size_t max_inflight = (size_t)std::max(1, d->params.max_inflight_tasks);
     uint64_t idle_spins = 0;
+    int burst = 0;  // submissions since the completion queues were last polled
     while (true) {
         bool progressed = false;
         // 1. stalled tasks go first (they hold the oldest priorities), then the new one
-        if (cur == nullptr && !d->stalled.empty() && d->inflight.size() < max_inflight) {
+        if (cur == nullptr && !d->stalled.empty() && d->inflight_count < max_inflight) {
             cur = d->stalled.front();
             d->stalled.pop_front();
         }
-        if (cur == nullptr && d->inflight.size() < max_inflight) {
+        if (cur == nullptr && d->inflight_count < max_inflight) {
             std::lock_guard<std::mutex> g(d->pending_lock);
             if (!d->pending.empty()) {
                 cur = d->pending.front();
@@ -743,11 +748,14 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
             if (r == 0) {
                 progressed = true;
                 cur = nullptr;
+                // keep feeding the streams: poll completions only every few submissions (each poll is one
+                // cudaEventQuery per stream), a submission is what keeps the copy engines and SMs busy
+                if (++burst < 8) continue;
             } else if (r == 1) {
                 d->stats.nb_stalls++;
                 // no room: write dirty tiles back so that they become evictable, then wait for completions
                 bool w = start_w2r(d);
-                if (!w && d->inflight.empty()) {
+                if (!w && d->inflight_count == 0) {
                     fprintf(stderr,
                             "[parsec_b200] task needs more device memory than can ever be freed (%zu bytes in use)\n",
                             d->heap->in_use());
@@ -777,11 +785,12 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
             }
         }
         // 2. retire whatever finished
+        burst = 0;
         if (progress_completions(d)) progressed = true;
         // 3. leave when the device is drained (:2742-2753)
         if (d->mutex.load() == 0) break;
         if (!progressed) {
-            if (++idle_spins > 64 && d->inflight.empty() && d->stalled.empty()) {
+            if (++idle_spins > 64 && d->inflight_count == 0 && d->stalled.empty()) {
                 // tasks counted in mutex but not yet visible in pending (a submitter between its two steps)
                 std::this_thread::yield();
             }

@@ -254,6 +254,19 @@ dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ C
     const int g = lane >> 2, t = lane & 3;
     const int wm = warp & 1, wn = warp >> 1;
 
+    if (beta != 0.0) {
+        // pull the old C tile towards L2 while the main loop runs: lane c takes column c of the warp tile, whose
+        // 64 rows are four 128-byte lines
+        const int col = n0 + wn * 32 + lane;
+        const int rowb = m0 + wm * 64;
+        if (col < N && rowb < M) {
+            const double* cp = C + (size_t)rowb + (size_t)col * ldc;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (rowb + 16 * i < M) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(cp + 16 * i));
+        }
+    }
+
     // per-thread shared-memory offsets (bytes, relative to the stage base)
     const uint32_t a_thread = (uint32_t)((4 * wm + (g >> 1)) * 2048 + t * 128);
     uint32_t a_off[2][4];

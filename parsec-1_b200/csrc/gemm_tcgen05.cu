@@ -21,6 +21,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "pb2_internal.h"
@@ -29,13 +30,15 @@
 namespace pb2 {
 
 constexpr int G_BM = 128, G_BN = 256, G_BK = 64;
-constexpr int G_STAGES = 4;
+// ring depth: 4 stages with one CTA per SM, or 2 stages with two CTAs per SM (2 x 256 TMEM columns), where one CTA's
+// epilogue (the C tile streams in and out once per task) runs under the other CTA's main loop
+constexpr int G_STAGES_1CTA = 4, G_STAGES_2CTA = 2;
 constexpr int G_A_BYTES = G_BM * G_BK * 2;  // 16 KiB: two [64 k][64 m] boxes
 constexpr int G_B_BYTES = G_BN * G_BK * 2;  // 32 KiB: one [256 n][64 k] box
 constexpr int G_STAGE_BYTES = G_A_BYTES + G_B_BYTES;
 constexpr int G_THREADS = 192;
 constexpr int G_TMEM_COLS = 256;
-constexpr size_t G_SMEM = (size_t)G_STAGES * G_STAGE_BYTES + 1024 + 256;
+constexpr size_t gemm_smem(int stages) { return (size_t)stages * G_STAGE_BYTES + 1024 + 256; }
 
 // instruction descriptor, kind::f16 (cute/arch/mma_sm100_desc.hpp InstrDescriptor):
 //   [4,6) c_format = 1 (F32); [7,10) a_format = 1 (BF16); [10,13) b_format = 1 (BF16);
@@ -94,7 +97,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
-__global__ void __launch_bounds__(G_THREADS, 1)
+template <int G_STAGES>
+__global__ void __launch_bounds__(G_THREADS, G_STAGES <= 2 ? 2 : 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
                   float alpha, float beta, float* __restrict__ C, int ldc) {
     extern __shared__ uint8_t smem_raw[];
@@ -173,6 +177,13 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         // epilogue: TMEM -> registers -> global (column-major, 128-byte coalesced per column)
         const int quarter = warp & 3;
         const int row = m0 + quarter * 32 + lane;
+        if (beta != 0.0f && m0 + quarter * 32 < M) {
+            // pull this warp's 32-row strip of the old C tile towards L2 while the main loop runs: for one column the
+            // strip is one 128-byte line; lane j takes columns j, j+32, ...
+            const float* strip = C + (size_t)(m0 + quarter * 32);
+            for (int c = lane; c < G_BN && n0 + c < N; c += 32)
+                asm volatile("prefetch.global.L2 [%0];\n" ::"l"(strip + (size_t)(n0 + c) * ldc));
+        }
         if (KT > 0) {
             mbar_wait(tmem_full, 0);
             tc_fence_after();
@@ -188,15 +199,21 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 for (int j = 0; j < 32; ++j) v[j] = 0u;
             }
             if (row < M) {
+                float* base = C + (size_t)row + (size_t)(n0 + c0) * ldc;
+                const int ncols = min(32, N - (n0 + c0));
+                if (beta != 0.0f) {
+                    // all 32 loads of the chunk are issued before the first use: one DRAM round trip per chunk
+                    // instead of one per column
+                    float old[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int col = n0 + c0 + j;
-                    if (col < N) {
-                        float* p = C + (size_t)row + (size_t)col * ldc;
-                        float r = alpha * __uint_as_float(v[j]);
-                        if (beta != 0.0f) r += beta * *p;
-                        *p = r;
-                    }
+                    for (int j = 0; j < 32; ++j) old[j] = (j < ncols) ? __ldcs(base + (size_t)j * ldc) : 0.0f;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]) + beta * old[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]);
                 }
             }
         }
@@ -257,9 +274,18 @@ extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int 
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return PB2_ERR_CUDA;
     if (dev < 64 && !g_gemm_attr_set[dev]) {
-        if (cudaFuncSetAttribute(gemm_bf16_tcgen05, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM) != cudaSuccess)
+        if (cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_1CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)gemm_smem(G_STAGES_1CTA)) != cudaSuccess ||
+            cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_2CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)gemm_smem(G_STAGES_2CTA)) != cudaSuccess)
             return PB2_ERR_CUDA;
         g_gemm_attr_set[dev] = true;
+    }
+    // PB2_GEMM_BF16_CTAS=1 selects the deep single-CTA ring (kept for A/B runs); default: two CTAs per SM
+    static int ctas = -1;
+    if (ctas < 0) {
+        const char* e = getenv("PB2_GEMM_BF16_CTAS");
+        ctas = (e && e[0] == '1') ? 1 : 2;
     }
     CUtensorMap ma, mb;
     if (k > 0 && (bf16_tmap(&ma, A, m, k, lda, 0) || bf16_tmap(&mb, B, k, n, ldb, 1))) return PB2_ERR_CUDA;
@@ -268,6 +294,11 @@ extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int 
         memset(&mb, 0, sizeof(mb));
     }
     dim3 grid(((m + G_BM - 1) / G_BM) * ((n + G_BN - 1) / G_BN));
-    gemm_bf16_tcgen05<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+    if (ctas == 1)
+        gemm_bf16_tcgen05<G_STAGES_1CTA><<<grid, G_THREADS, gemm_smem(G_STAGES_1CTA), (cudaStream_t)stream>>>(
+            ma, mb, m, n, k, alpha, beta, C, ldc);
+    else
+        gemm_bf16_tcgen05<G_STAGES_2CTA><<<grid, G_THREADS, gemm_smem(G_STAGES_2CTA), (cudaStream_t)stream>>>(
+            ma, mb, m, n, k, alpha, beta, C, ldc);
     return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
 }

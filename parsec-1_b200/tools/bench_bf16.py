@@ -1,7 +1,7 @@
-"""Times parsec_b200_gemm_bf16_sm100 against torch.matmul (cuBLAS) on bf16 inputs.  python parsec-1_b200/tools/bench_bf16.py"""
+"""Times parsec_b200_gemm_bf16_sm100 against torch.matmul (cuBLAS) on bf16 inputs, alone and as a stream of tile tasks.
+python parsec-1_b200/tools/bench_bf16.py            (PB2_GEMM_BF16_CTAS=1 selects the one-CTA-per-SM variant)"""
 import importlib.util
 import os
-import sys
 
 import torch
 
@@ -10,6 +10,7 @@ spec = importlib.util.spec_from_file_location("hostapi", os.path.join(ROOT, "par
 H = importlib.util.module_from_spec(spec)
 spec.loader.exec_module(H)
 L = H.lib()
+print("variant: PB2_GEMM_BF16_CTAS=%s" % os.environ.get("PB2_GEMM_BF16_CTAS", "2 (default)"))
 
 
 def timed(fn, reps):
@@ -32,12 +33,39 @@ for n in (2048, 4096, 8192):
     B = (torch.rand(n, n, device="cuda") - 0.5).to(torch.bfloat16)
     C = torch.zeros(n, n, device="cuda", dtype=torch.float32)
     s = torch.cuda.current_stream().cuda_stream
-    ours = timed(lambda: L.parsec_b200_gemm_bf16_sm100(b"N", b"N", n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0,
-                                                       C.data_ptr(), n, s), 20 if n <= 4096 else 5)
-    # column-major C = A B with column-major A, B is row-major C^T = B^T A^T: same flops for cuBLAS
-    ref = timed(lambda: torch.matmul(B, A), 20 if n <= 4096 else 5)
-    got = C.clone()
-    want = torch.matmul(B.float(), A.float())   # row-major view of (A_cm * B_cm)^T
-    err = (got - want).abs().max().item()
-    print("n=%5d ours %.3f ms %.1f TFLOP/s | cuBLAS bf16 %.3f ms %.1f TFLOP/s | max|diff vs fp32 matmul| %.3e" % (
-        n, ours, 2 * n ** 3 / ours * 1e-9, ref, 2 * n ** 3 / ref * 1e-9, err))
+    reps = 20 if n <= 4096 else 5
+    for beta in (0.0, 1.0):
+        ours = timed(lambda: L.parsec_b200_gemm_bf16_sm100(b"N", b"N", n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, beta,
+                                                           C.data_ptr(), n, s), reps)
+        print("n=%5d beta=%.0f ours %.3f ms %.1f TFLOP/s" % (n, beta, ours, 2 * n ** 3 / ours * 1e-9))
+    ref = timed(lambda: torch.matmul(B, A), reps)
+    print("n=%5d        cuBLAS bf16 %.3f ms %.1f TFLOP/s" % (n, ref, 2 * n ** 3 / ref * 1e-9))
+
+# a stream of independent 2048^3 tile tasks (C += A B), S streams round-robin: the shape the device module produces
+nb, ntile = 2048, 24
+As = [(torch.rand(nb, nb, device="cuda") - 0.5).to(torch.bfloat16) for _ in range(ntile)]
+Bs = [(torch.rand(nb, nb, device="cuda") - 0.5).to(torch.bfloat16) for _ in range(ntile)]
+Cs = [torch.zeros(nb, nb, device="cuda", dtype=torch.float32) for _ in range(ntile)]
+for S in (1, 2, 4):
+    streams = [torch.cuda.Stream() for _ in range(S)]
+
+    def run():
+        for i in range(ntile * 4):
+            t = i % ntile
+            L.parsec_b200_gemm_bf16_sm100(b"N", b"N", nb, nb, nb, 1.0, As[t].data_ptr(), nb, Bs[t].data_ptr(), nb, 1.0,
+                                          Cs[t].data_ptr(), nb, streams[i % S].cuda_stream)
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(3):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for st in streams:
+            st.wait_event(e0)
+        run()
+        for st in streams:
+            torch.cuda.current_stream().wait_stream(st)
+        e1.record()
+        e1.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    print("tile stream S=%d: %d x 2048^3 (beta=1) in %.3f ms -> %.1f TFLOP/s" % (S, ntile * 4, best, 2 * nb ** 3 * ntile * 4 / best * 1e-9))
