@@ -144,6 +144,8 @@ def main():
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--replicas", action="store_true",
+                    help="diagnostic for N>1: independent 1x1 problems per GPU (isolates box effects from the data plane)")
     ap.add_argument("--dtype", default="f64", choices=["f64", "bf16"],
                     help="f64: the headline DGEMM; bf16: BF16-in/FP32-acc tiles on tcgen05 (BASELINE configs[4], use --nb 2048)")
     args = ap.parse_args()
@@ -168,7 +170,10 @@ def main():
     # weak scaling: flops per GPU constant, N_g = N_1 * g^(1/3) rounded to a whole number of tiles
     N = args.n if world == 1 else int(round(args.n * world ** (1.0 / 3.0) / NB)) * NB
     P, Q = H.grid_for(world)
-    comm = H.Comm(local_rank, P, Q, rank) if world > 1 else None
+    if args.replicas:   # diagnostic: every rank runs its own 1x1 problem, no data-plane traffic at all
+        N, P, Q = args.n, 1, 1
+    grid_rank = 0 if args.replicas else rank
+    comm = H.Comm(local_rank, P, Q, rank) if (world > 1 and not args.replicas) else None
     bf16 = args.dtype == "bf16"
     mtypes = (H.MATRIX_BF16, H.MATRIX_BF16, H.MATRIX_FLOAT) if bf16 else (H.MATRIX_DOUBLE,) * 3
     if bf16:
@@ -184,7 +189,7 @@ def main():
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0)
     mats, bufs = [], []
     for seed, mtype in zip((1789, 1805, 1901), mtypes):
-        m = H.Matrix(mtype, N, N, NB, NB, P, Q, rank)
+        m = H.Matrix(mtype, N, N, NB, NB, P, Q, grid_rank)
         b = torch.empty(max(m.nbytes, 8), dtype=torch.uint8, pin_memory=True)   # cudaHostAlloc: the collection's host memory
         m.set_buffer(b)
         m.fill_lcg(seed, dev)
@@ -222,8 +227,11 @@ def main():
     # warm-up: W steps (the first stages every tile into HBM; the rest run from the cache)
     for _ in range(max(3, args.warmup)):
         H.tiled_gemm(A, B, Cm, dev, **knobs)
+    # only rank 0 polls nvidia-smi: every query takes driver locks, and eight pollers at 5 Hz measurably slowed the
+    # submission path of all ranks (profiles/bench_r1_g8_notes.md)
     sampler = ClockSampler(local_rank)
-    sampler.start()
+    if rank == 0:
+        sampler.start()
     dev.stats(reset=True)
     ms_resident = timed(args.steps, flush=False)
     st_resident = dev.stats(reset=True)
@@ -245,7 +253,7 @@ def main():
     dev = H.Device(local_rank, **dev2_params)
     mats = []
     for b, mtype in zip(bufs, mtypes):
-        m = H.Matrix(mtype, N, N, NB, NB, P, Q, rank)
+        m = H.Matrix(mtype, N, N, NB, NB, P, Q, grid_rank)
         m.set_buffer(b)
         mats.append(m)
     A, B, Cm = mats
@@ -261,6 +269,8 @@ def main():
         achieved_tf = per_launch_flops * nstreams / (avg_ms * 1e-3) * 1e-12
         prof = {"avg_launch_ms": avg_ms, "samples": int(len(lms)), "resident_launches": nstreams}
 
+    if args.replicas:
+        flops *= world
     value = flops / (ms_resident * 1e-3) * 1e-9          # whole job: one N x N x N product spread over all ranks
     e2e = flops / (ms_e2e * 1e-3) * 1e-9
     tile_bytes = NB * NB * 8
@@ -274,7 +284,7 @@ def main():
                                 "(BASELINE configs[1])" % (N, NB)) if world == 1 else
                                ("tiled DGEMM N=%d NB=%d fp64, 2D block-cyclic %dx%d over %d B200 with NCCL tile bcast "
                                 "(BASELINE configs[2] shape; weak scaling from N=%d)" % (N, NB, P, Q, world, args.n)),
-                   "tasks_per_step": (N // NB) ** 3,
+                   "tasks_per_step": (N // NB) ** 3, "host_cores": os.cpu_count(), "replicas_diagnostic": bool(args.replicas),
                    "l2": "inputs (%.1f GiB) far larger than L2" % (N * N * (8 if bf16 else 24) / 2 ** 30),
                    "parallelism": "1 process per GPU, %dx%d grid; %d exec streams per GPU" % (P, Q, args.streams - 2),
                    "pct_of_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
@@ -283,6 +293,8 @@ def main():
                 "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps),
                 "nvlink_bytes_in_per_step_rank0": st_e2e["data_in_from_peers"] // max(1, args.steps)},
         "gpu_launches": st_resident["kernel_launches"],
+        "host_us_per_task": {"submit": st_resident["host_submit_ns"] / 1e3 / max(1, st_resident["kernel_launches"]),
+                             "retire": st_resident["host_retire_ns"] / 1e3 / max(1, st_resident["kernel_launches"])},
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": (achieved_tf / peak_tf) if prof else None,

@@ -74,6 +74,11 @@ int parsec_b200_dgemm(char transa, char transb, int m, int n, int k, double alph
 int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A, int lda,
                                 const void* B, int ldb, float beta, float* C, int ldc, void* stream);
 
+/* Same kernel with fp32 operands consumed as TF32 (kind::tf32; the low 13 mantissa bits of A and B are ignored) and
+ * fp32 accumulation: the cublasSgemm shape under CUBLAS_COMPUTE_32F_FAST_TF32.  Leading dimensions: multiples of 4. */
+int parsec_b200_gemm_tf32_sm100(char transa, char transb, int m, int n, int k, float alpha, const float* A, int lda,
+                                const float* B, int ldb, float beta, float* C, int ldc, void* stream);
+
 /* HBM heap: zone_malloc_init / zone_malloc / zone_free / zone_in_use (parsec/utils/zone_malloc.h:41-63).  The device
  * module owns one per GPU; these handles let a test compare placement decisions with the reference allocator
  * offset by offset, without a GPU (the base address is symbolic). */
@@ -136,6 +141,7 @@ typedef struct pb2_device_stats_s {
     uint64_t required_data_in, required_data_out, nb_data_faults;
     uint64_t nb_evictions, nb_w2r_tasks, nb_w2r_tiles, nb_stalls, kernel_launches;
     uint64_t hbm_bytes_total, hbm_bytes_in_use;
+    uint64_t host_submit_ns, host_retire_ns; /* manager-thread time spent submitting / retiring tasks */
 } pb2_device_stats_t;
 int pb2_device_get_stats(pb2_device_t* dev, pb2_device_stats_t* out, int reset);
 

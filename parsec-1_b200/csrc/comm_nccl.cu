@@ -32,6 +32,8 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t);
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
     const char* (*GetErrorString)(ncclResult_t);
+    ncclResult_t (*GroupStart)();
+    ncclResult_t (*GroupEnd)();
     bool ok = false;
 };
 static NcclApi* nccl_api() {
@@ -51,7 +53,10 @@ static NcclApi* nccl_api() {
     api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
     api.Broadcast = (decltype(api.Broadcast))dlsym(h, "ncclBroadcast");
     api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
-    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString;
+    api.GroupStart = (decltype(api.GroupStart))dlsym(h, "ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd))dlsym(h, "ncclGroupEnd");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString &&
+             api.GroupStart && api.GroupEnd;
     return api.ok ? &api : nullptr;
 }
 
@@ -83,7 +88,11 @@ extern "C" int pb2_comm_create(int cuda_index, int P, int Q, int rank, const voi
     if (cudaSetDevice(cuda_index) != cudaSuccess) return PB2_ERR_DEVICE;
     pb2_comm_s* c = new pb2_comm_s();
     c->P = P; c->Q = Q; c->rank = rank; c->myrow = rank / Q; c->mycol = rank % Q; c->cuda_index = cuda_index;
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return PB2_ERR_DEVICE; }
+    // highest priority: the exec streams always have tile kernels queued, and a broadcast kernel that has to wait for
+    // SM slots behind them turns the data plane into the critical path
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { delete c; return PB2_ERR_DEVICE; }
     ncclUniqueId rid, cid;
     if (Q > 1) {
         if (!row_id) { delete c; return PB2_ERR_BAD_PARAM; }
@@ -108,6 +117,15 @@ extern "C" int pb2_comm_destroy(pb2_comm_t* c) {
     cudaStreamDestroy(c->stream);
     delete c;
     return PB2_SUCCESS;
+}
+
+// ncclGroupStart / ncclGroupEnd around the broadcasts of one GEMM step: NCCL fuses them into one launch per
+// communicator instead of one kernel per tile
+extern "C" int pb2_comm_group_begin(pb2_comm_t* c) {
+    return (c && nccl_api() && nccl_api()->GroupStart() == ncclSuccess) ? PB2_SUCCESS : PB2_ERR_DEVICE;
+}
+extern "C" int pb2_comm_group_end(pb2_comm_t* c) {
+    return (c && nccl_api() && nccl_api()->GroupEnd() == ncclSuccess) ? PB2_SUCCESS : PB2_ERR_DEVICE;
 }
 
 extern "C" void* pb2_comm_stream(pb2_comm_t* c) { return c ? (void*)c->stream : nullptr; }

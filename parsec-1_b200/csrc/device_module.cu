@@ -744,7 +744,10 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
             }
         }
         if (cur) {
+            auto ts0 = std::chrono::steady_clock::now();
             int r = try_submit(d, cur);
+            d->stats.host_submit_ns +=
+                (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - ts0).count();
             if (r == 0) {
                 progressed = true;
                 cur = nullptr;
@@ -786,7 +789,15 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
         }
         // 2. retire whatever finished
         burst = 0;
-        if (progress_completions(d)) progressed = true;
+        {
+            auto tr0 = std::chrono::steady_clock::now();
+            bool any = progress_completions(d);
+            if (any) {
+                progressed = true;
+                d->stats.host_retire_ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
+                                               std::chrono::steady_clock::now() - tr0).count();
+            }
+        }
         // 3. leave when the device is drained (:2742-2753)
         if (d->mutex.load() == 0) break;
         if (!progressed) {

@@ -26,6 +26,7 @@
 #include "tma_utils.cuh"
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 namespace pb2 {
 
@@ -487,9 +488,11 @@ struct TmapEntry {
     bool valid;
 };
 static int get_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int kind) {
-    static thread_local TmapEntry cache[512];
+    // 16 Ki entries: a 24 GiB working set of 8 MiB tiles is 3 Ki distinct (pointer, shape) keys
+    static thread_local std::vector<TmapEntry> cache;
+    if (cache.empty()) cache.resize(16384);
     uintptr_t h = ((uintptr_t)p >> 9) * 0x9E3779B97F4A7C15ull + (uintptr_t)(d0 * 31 + d1 * 17 + ld * 7 + kind);
-    TmapEntry& e = cache[(h >> 20) & 511];
+    TmapEntry& e = cache[(h >> 20) & 16383];
     if (e.valid && e.k.p == p && e.k.d0 == d0 && e.k.d1 == d1 && e.k.ld == ld && e.k.kind == kind) {
         *out = e.m;
         return 0;

@@ -23,38 +23,39 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 #include "pb2_internal.h"
 #include "tma_utils.cuh"
 
 namespace pb2 {
 
-constexpr int G_BM = 128, G_BN = 256, G_BK = 64;
+constexpr int G_BM = 128, G_BN = 256;
 // ring depth: 4 stages with one CTA per SM, or 2 stages with two CTAs per SM (2 x 256 TMEM columns), where one CTA's
 // epilogue (the C tile streams in and out once per task) runs under the other CTA's main loop
 constexpr int G_STAGES_1CTA = 4, G_STAGES_2CTA = 2;
-constexpr int G_A_BYTES = G_BM * G_BK * 2;  // 16 KiB: two [64 k][64 m] boxes
-constexpr int G_B_BYTES = G_BN * G_BK * 2;  // 32 KiB: one [256 n][64 k] box
+constexpr int G_A_BYTES = G_BM * 128;  // 16 KiB: 128 rows of m by 128 bytes of k, as boxes [k][one 128-byte row of m]
+constexpr int G_B_BYTES = G_BN * 128;  // 32 KiB: one box [256 n][128 bytes of k]
 constexpr int G_STAGE_BYTES = G_A_BYTES + G_B_BYTES;
 constexpr int G_THREADS = 192;
 constexpr int G_TMEM_COLS = 256;
 constexpr size_t gemm_smem(int stages) { return (size_t)stages * G_STAGE_BYTES + 1024 + 256; }
 
-// instruction descriptor, kind::f16 (cute/arch/mma_sm100_desc.hpp InstrDescriptor):
-//   [4,6) c_format = 1 (F32); [7,10) a_format = 1 (BF16); [10,13) b_format = 1 (BF16);
+// instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor), built per element type in the kernel:
+//   [4,6) c_format = 1 (F32); [7,10) a_format, [10,13) b_format = 1 (BF16) or 2 (TF32);
 //   [15] a_major = 1 (MN-major); [16] b_major = 0 (K-major); [17,23) N >> 3; [24,29) M >> 4
-constexpr uint32_t G_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((uint32_t)(G_BN >> 3) << 17) |
-                             ((uint32_t)(G_BM >> 4) << 24);
 
 // shared-memory matrix descriptor (SmemDescriptor): [0,14) start >> 4; [16,30) LBO >> 4; [32,46) SBO >> 4;
 // [46,48) version = 1; [61,64) layout type = 2 (SWIZZLE_128B)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte chunks XOR row, 8-row atom), 1 = SWIZZLE_128B_BASE32B (32-byte chunks XOR row,
+// 4-row atom) -- the only layout the hardware accepts for an MN-major operand with 32-bit elements (TF32)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
     d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
     d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
     d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
+    d |= (uint64_t)layout << 61;
     return d;
 }
 
@@ -78,6 +79,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // arrives on the mbarrier once every MMA issued so far by this thread has completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar))
@@ -97,10 +108,20 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
-template <int G_STAGES>
+// EB = operand element size: 2 = bf16 (kind::f16), 4 = fp32 consumed as TF32 (kind::tf32).  A stage is 128 bytes deep
+// along K for B (64 bf16 or 32 fp32) and always 48 KiB; an UMMA consumes 32 bytes of K (16 bf16 / 8 tf32).
+template <int G_STAGES, int EB>
 __global__ void __launch_bounds__(G_THREADS, G_STAGES <= 2 ? 2 : 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
                   float alpha, float beta, float* __restrict__ C, int ldc) {
+    constexpr int BKE = 128 / EB;             // K elements per stage
+    constexpr int MBOX = 128 / EB;            // m elements per A box (one 128-byte row)
+    constexpr int NBOX = G_BM / MBOX;         // A boxes per stage
+    constexpr int BOX_BYTES = BKE * 128;      // one A box: BKE k-rows of 128 bytes
+    constexpr int UK = 32 / EB;               // K elements per UMMA
+    constexpr uint32_t IDESC = (1u << 4) | ((EB == 2 ? 1u : 2u) << 7) | ((EB == 2 ? 1u : 2u) << 10) | (1u << 15) |
+                               ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24);
+    static_assert(NBOX * BOX_BYTES == G_A_BYTES && G_BN * 128 == G_B_BYTES, "stage layout");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t sbase0 = (raw + 1023u) & ~1023u;
@@ -113,7 +134,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_m = (M + G_BM - 1) / G_BM;
     const int m0 = (blockIdx.x % tiles_m) * G_BM, n0 = (blockIdx.x / tiles_m) * G_BN;
-    const int KT = (K + G_BK - 1) / G_BK;
+    const int KT = (K + BKE - 1) / BKE;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < G_STAGES; ++s) {
@@ -140,9 +161,10 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 if (kt >= G_STAGES) mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * G_STAGE_BYTES;
                 mbar_arrive_expect_tx(&full[stage], G_STAGE_BYTES);
-                tma_load_2d(sa, &mapA, m0, kt * G_BK, &full[stage]);
-                tma_load_2d(sa + G_A_BYTES / 2, &mapA, m0 + 64, kt * G_BK, &full[stage]);
-                tma_load_2d(sa + G_A_BYTES, &mapB, kt * G_BK, n0, &full[stage]);
+#pragma unroll
+                for (int b = 0; b < NBOX; ++b)
+                    tma_load_2d(sa + b * BOX_BYTES, &mapA, m0 + b * MBOX, kt * BKE, &full[stage]);
+                tma_load_2d(sa + G_A_BYTES, &mapB, kt * BKE, n0, &full[stage]);
                 if (++stage == G_STAGES) {
                     stage = 0;
                     phase ^= 1;
@@ -159,11 +181,14 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const uint32_t sa = sbase0 + stage * G_STAGE_BYTES;
                 const uint32_t sb = sa + G_A_BYTES;
 #pragma unroll
-                for (int k16 = 0; k16 < G_BK / 16; ++k16) {
-                    // A: 16 k-rows of 128 B further per step; B: 32 bytes further inside the 128-byte swizzle row
-                    const uint64_t adesc = umma_desc(sa + k16 * 2048, G_A_BYTES / 2, 1024);
-                    const uint64_t bdesc = umma_desc(sb + k16 * 32, 16, 1024);
-                    umma_bf16(tmem_base, adesc, bdesc, G_IDESC, (kt | k16) != 0);
+                for (int ku = 0; ku < BKE / UK; ++ku) {
+                    // A: UK k-rows of 128 B further per step (LBO = one box: the next 128 bytes of m);
+                    // B: 32 bytes further inside the 128-byte swizzle row
+                    const uint64_t adesc = EB == 2 ? umma_desc(sa + ku * UK * 128, BOX_BYTES, 1024, 2)
+                                                   : umma_desc(sa + ku * UK * 128, BOX_BYTES, 512, 1);
+                    const uint64_t bdesc = umma_desc(sb + ku * 32, 16, 1024);
+                    if (EB == 2) umma_bf16(tmem_base, adesc, bdesc, IDESC, (kt | ku) != 0);
+                    else umma_tf32(tmem_base, adesc, bdesc, IDESC, (kt | ku) != 0);
                 }
                 umma_commit(&empty[stage]);  // the stage may be refilled once these MMAs have read it
                 if (++stage == G_STAGES) {
@@ -226,8 +251,6 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     }
 }
 
-static bool g_gemm_attr_set[64] = {false};
-
 struct BfMapKey {
     const void* p;
     int d0, d1, ld, kind;
@@ -237,49 +260,54 @@ struct BfMapEntry {
     CUtensorMap m;
     bool valid;
 };
-static int bf16_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int kind) {
-    static thread_local BfMapEntry cache[512];
-    uintptr_t h = ((uintptr_t)p >> 9) * 0x9E3779B97F4A7C15ull + (uintptr_t)(d0 * 31 + d1 * 17 + ld * 7 + kind);
-    BfMapEntry& e = cache[(h >> 20) & 511];
-    if (e.valid && e.k.p == p && e.k.d0 == d0 && e.k.d1 == d1 && e.k.ld == ld && e.k.kind == kind) {
+// kind: 0 = A operand (boxes of one 128-byte row of m by one stage of k), 1 = B operand (one stage of k by G_BN columns)
+static int umma_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int kind, int eb) {
+    static thread_local std::vector<BfMapEntry> cache;
+    if (cache.empty()) cache.resize(16384);
+    const int tag = kind + 2 * eb;
+    uintptr_t h = ((uintptr_t)p >> 9) * 0x9E3779B97F4A7C15ull + (uintptr_t)(d0 * 31 + d1 * 17 + ld * 7 + tag);
+    BfMapEntry& e = cache[(h >> 20) & 16383];
+    if (e.valid && e.k.p == p && e.k.d0 == d0 && e.k.d1 == d1 && e.k.ld == ld && e.k.kind == tag) {
         *out = e.m;
         return 0;
     }
-    int rc = kind == 0 ? encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p, d0, d1, ld, 64, G_BK,
-                                        CU_TENSOR_MAP_SWIZZLE_128B)
-                       : encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p, d0, d1, ld, G_BK, G_BN,
-                                        CU_TENSOR_MAP_SWIZZLE_128B);
+    const CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const uint32_t row = 128 / eb;  // elements in one 128-byte swizzle row
+    // the MN-major fp32 (TF32) operand needs the 32-byte-atom flavour of the 128-byte swizzle (see umma_desc)
+    const CUtensorMapSwizzle swa = eb == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    int rc = kind == 0 ? encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, row, swa)
+                       : encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, G_BN, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) {
         e.valid = false;
         return rc;
     }
-    e.k = {p, d0, d1, ld, kind};
+    e.k = {p, d0, d1, ld, tag};
     e.valid = true;
     *out = e.m;
     return 0;
 }
 
-}  // namespace pb2
-
-extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A,
-                                           int lda, const void* B, int ldb, float beta, float* C, int ldc,
-                                           void* stream) {
-    using namespace pb2;
+template <int EB>
+static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float alpha, const void* A, int lda, const void* B,
+                            int ldb, float beta, float* C, int ldc, void* stream) {
     if ((transa != 'N' && transa != 'n') || (transb != 'N' && transb != 'n')) return PB2_ERR_NOT_SUPPORTED;
     if (m < 0 || n < 0 || k < 0 || lda < (m > 1 ? m : 1) || ldb < (k > 1 ? k : 1) || ldc < (m > 1 ? m : 1))
         return PB2_ERR_BAD_PARAM;
     if (m == 0 || n == 0) return PB2_SUCCESS;
     // TMA: 16-byte aligned bases and row pitches
-    if ((((uintptr_t)A | (uintptr_t)B) & 15) || (lda & 7) || (ldb & 7) || (((uintptr_t)C) & 3)) return PB2_ERR_NOT_SUPPORTED;
+    const int pitch_mask = 16 / EB - 1;
+    if ((((uintptr_t)A | (uintptr_t)B) & 15) || (lda & pitch_mask) || (ldb & pitch_mask) || (((uintptr_t)C) & 3))
+        return PB2_ERR_NOT_SUPPORTED;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return PB2_ERR_CUDA;
-    if (dev < 64 && !g_gemm_attr_set[dev]) {
-        if (cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_1CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static bool attr_set[64] = {false};
+    if (dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_1CTA, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)gemm_smem(G_STAGES_1CTA)) != cudaSuccess ||
-            cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_2CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            cudaFuncSetAttribute(gemm_bf16_tcgen05<G_STAGES_2CTA, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)gemm_smem(G_STAGES_2CTA)) != cudaSuccess)
             return PB2_ERR_CUDA;
-        g_gemm_attr_set[dev] = true;
+        attr_set[dev] = true;
     }
     // PB2_GEMM_BF16_CTAS=1 selects the deep single-CTA ring (kept for A/B runs); default: two CTAs per SM
     static int ctas = -1;
@@ -288,17 +316,33 @@ extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int 
         ctas = (e && e[0] == '1') ? 1 : 2;
     }
     CUtensorMap ma, mb;
-    if (k > 0 && (bf16_tmap(&ma, A, m, k, lda, 0) || bf16_tmap(&mb, B, k, n, ldb, 1))) return PB2_ERR_CUDA;
+    if (k > 0 && (umma_tmap(&ma, A, m, k, lda, 0, EB) || umma_tmap(&mb, B, k, n, ldb, 1, EB))) return PB2_ERR_CUDA;
     if (k == 0) {  // nothing to stage: the kernel only scales C; the maps are never dereferenced
         memset(&ma, 0, sizeof(ma));
         memset(&mb, 0, sizeof(mb));
     }
     dim3 grid(((m + G_BM - 1) / G_BM) * ((n + G_BN - 1) / G_BN));
     if (ctas == 1)
-        gemm_bf16_tcgen05<G_STAGES_1CTA><<<grid, G_THREADS, gemm_smem(G_STAGES_1CTA), (cudaStream_t)stream>>>(
+        gemm_bf16_tcgen05<G_STAGES_1CTA, EB><<<grid, G_THREADS, gemm_smem(G_STAGES_1CTA), (cudaStream_t)stream>>>(
             ma, mb, m, n, k, alpha, beta, C, ldc);
     else
-        gemm_bf16_tcgen05<G_STAGES_2CTA><<<grid, G_THREADS, gemm_smem(G_STAGES_2CTA), (cudaStream_t)stream>>>(
+        gemm_bf16_tcgen05<G_STAGES_2CTA, EB><<<grid, G_THREADS, gemm_smem(G_STAGES_2CTA), (cudaStream_t)stream>>>(
             ma, mb, m, n, k, alpha, beta, C, ldc);
     return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+}  // namespace pb2
+
+extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A,
+                                           int lda, const void* B, int ldb, float beta, float* C, int ldc,
+                                           void* stream) {
+    return pb2::launch_umma_gemm<2>(transa, transb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+}
+
+// fp32 operands consumed by the tensor cores as TF32 (the low 13 mantissa bits of A and B are ignored), fp32 accumulate:
+// the cublasSgemm shape with CUBLAS_COMPUTE_32F_FAST_TF32.
+extern "C" int parsec_b200_gemm_tf32_sm100(char transa, char transb, int m, int n, int k, float alpha, const float* A,
+                                           int lda, const float* B, int ldb, float beta, float* C, int ldc,
+                                           void* stream) {
+    return pb2::launch_umma_gemm<4>(transa, transb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, stream);
 }

@@ -31,7 +31,7 @@ class DeviceStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "executed_tasks data_in_from_host data_in_from_peers data_out_to_host required_data_in required_data_out "
         "nb_data_faults nb_evictions nb_w2r_tasks nb_w2r_tiles nb_stalls kernel_launches hbm_bytes_total "
-        "hbm_bytes_in_use").split()]
+        "hbm_bytes_in_use host_submit_ns host_retire_ns").split()]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -79,6 +79,8 @@ def lib():
         "parsec_b200_dgemm_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, dbl, vp, i32, vp, i32, dbl, vp, i32, vp]),
         "parsec_b200_dgemm": (i32, [C.c_char, C.c_char, i32, i32, i32, dbl, vp, i32, vp, i32, dbl, vp, i32, vp]),
         "parsec_b200_gemm_bf16_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, C.c_float, vp, i32, vp, i32,
+                                               C.c_float, vp, i32, vp]),
+        "parsec_b200_gemm_tf32_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, C.c_float, vp, i32, vp, i32,
                                                C.c_float, vp, i32, vp]),
         "pb2_zone_create": (vp, [i32, sz]), "pb2_zone_destroy": (None, [vp]), "pb2_zone_malloc": (i64, [vp, sz]),
         "pb2_zone_free": (i32, [vp, i64]), "pb2_zone_in_use": (sz, [vp]),
