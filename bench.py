@@ -144,6 +144,9 @@ def main():
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--hbm-gib", type=float, default=0.0,
+                    help="cap the HBM tile heap (GiB) to run out of core: the BASELINE configs[3] mechanism (LRU evict + "
+                         "write-back) at a size the box's host memory allows; 0 = 95%% of free HBM")
     ap.add_argument("--replicas", action="store_true",
                     help="diagnostic for N>1: independent 1x1 problems per GPU (isolates box effects from the data plane)")
     ap.add_argument("--dtype", default="f64", choices=["f64", "bf16"],
@@ -186,7 +189,8 @@ def main():
         peak_tf = fp64_peak_tflops(torch)
         peak_src = ("measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10; MEASURED_PEAKS.json has no fp64 entry "
                     "(DMMA issue peak measured 37.1 TFLOP/s, profiles/microbench_r1_v2_tma.log)")
-    dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0)
+    hbm = {"memory_number_of_blocks": int(args.hbm_gib * 2048)} if args.hbm_gib > 0 else {}   # 512 KiB blocks
+    dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0, **hbm)
     mats, bufs = [], []
     for seed, mtype in zip((1789, 1805, 1901), mtypes):
         m = H.Matrix(mtype, N, N, NB, NB, P, Q, grid_rank)
@@ -241,7 +245,7 @@ def main():
 
     # roofline of the dominant kernel (dgemm_nn_tma): per-launch durations from CUDA events on the exec streams, taken
     # in one extra resident step so that the event records do not sit inside the timed region above
-    dev2_params = dict(max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=1)
+    dev2_params = dict(max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=1, **hbm)
     prof = None
     if rank == 0:
         H.lib().pb2_device_memory_release(dev.h)
@@ -293,6 +297,11 @@ def main():
                 "d2h_bytes_per_step": st_e2e["data_out_to_host"] // max(1, args.steps),
                 "nvlink_bytes_in_per_step_rank0": st_e2e["data_in_from_peers"] // max(1, args.steps)},
         "gpu_launches": st_resident["kernel_launches"],
+        "hbm_cache": {"heap_gib": st_resident["hbm_bytes_total"] / 2 ** 30,
+                      "evictions_per_step": st_resident["nb_evictions"] // max(1, args.steps),
+                      "writeback_tiles_per_step": st_resident["nb_w2r_tiles"] // max(1, args.steps),
+                      "stalls_per_step": st_resident["nb_stalls"] // max(1, args.steps),
+                      "h2d_bytes_per_resident_step": st_resident["data_in_from_host"] // max(1, args.steps)},
         "host_us_per_task": {"submit": st_resident["host_submit_ns"] / 1e3 / max(1, st_resident["kernel_launches"]),
                              "retire": st_resident["host_retire_ns"] / 1e3 / max(1, st_resident["kernel_launches"])},
         "clocks": clocks,

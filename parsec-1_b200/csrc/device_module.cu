@@ -203,10 +203,15 @@ static void release_copy(pb2_device_s* d, pb2_copy_t* c) {  // detach + give the
 extern "C" int pb2_device_memory_release(pb2_device_t* d) {
     if (!d) return PB2_ERR_BAD_PARAM;
     if (d->mutex.load() != 0) return PB2_ERROR;  // a manager is active
+    std::vector<pb2_copy_t*> busy;
     while (pb2_copy_t* c = d->lru.pop_front()) {
-        if (c->readers != 0) continue;
+        if (c->readers != 0) {  // pinned by a reader (e.g. the comm layer): keep it
+            busy.push_back(c);
+            continue;
+        }
         release_copy(d, c);
     }
+    for (pb2_copy_t* c : busy) d->lru.push_back(c);
     return PB2_SUCCESS;
 }
 
