@@ -117,6 +117,8 @@ typedef struct pb2_device_params_s {
     int max_inflight_tasks;       /* tasks enqueued on the GPU but not completed (reference: 4 per stream, device_gpu.h:22) */
     int trace_events;             /* record pb2_event_t for every data-state transition */
     int profile_launches;         /* time every body launch with CUDA events on its exec stream (bench.py roofline) */
+    int sort_pending_tasks;       /* device_cuda_sort_pending_tasks (0): among the first 10 pending tasks take the one
+                                     that needs the fewest new tiles (parsec_gpu_sort_pending_list, device_gpu.c:117-166) */
 } pb2_device_params_t;
 void pb2_device_params_default(pb2_device_params_t* p);
 

@@ -106,6 +106,7 @@ extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->max_inflight_tasks = 256;
     p->trace_events = 0;
     p->profile_launches = 0;
+    p->sort_pending_tasks = 0;
 }
 
 static cudaEvent_t get_event(pb2_device_s* d) {
@@ -744,8 +745,27 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
         if (cur == nullptr && d->inflight_count < max_inflight) {
             std::lock_guard<std::mutex> g(d->pending_lock);
             if (!d->pending.empty()) {
-                cur = d->pending.front();
-                d->pending.pop_front();
+                size_t pick = 0;
+                if (d->params.sort_pending_tasks) {
+                    // parsec_gpu_sort_pending_list: look at the first 10 and prefer the task that has to bring in the
+                    // fewest tiles (parsec_gpu_check_space_needed counts flows without a device copy)
+                    int best = 1 << 30;
+                    const size_t span = std::min<size_t>(10, d->pending.size());
+                    for (size_t i = 0; i < span; ++i) {
+                        const pb2_gpu_task_t* c = d->pending[i];
+                        int missing = 0;
+                        for (int f = 0; f < c->nb_flows; ++f)
+                            if (c->flow_data[f] && (c->flow_access[f] & PB2_FLOW_ACCESS_RW) &&
+                                !c->flow_data[f]->device_copies[d->device_index])
+                                ++missing;
+                        if (missing < best) {
+                            best = missing;
+                            pick = i;
+                        }
+                    }
+                }
+                cur = d->pending[pick];
+                d->pending.erase(d->pending.begin() + pick);
             }
         }
         if (cur) {

@@ -76,6 +76,10 @@ static int gemm_submit(pb2_device_t* dev, pb2_gpu_task_t* t, void* stream) {
         rc = parsec_b200_dgemm('N', 'N', rm, rn, rk, 1.0, (const double*)t->flow_dev_ptr[0], tp->gA.mb,
                                (const double*)t->flow_dev_ptr[1], tp->gB.mb, 1.0, (double*)t->flow_dev_ptr[2], tp->gC.mb,
                                stream);
+    } else if (tp->gA.mtype == PB2_MATRIX_FLOAT) {
+        rc = parsec_b200_gemm_tf32_sm100('N', 'N', rm, rn, rk, 1.0f, (const float*)t->flow_dev_ptr[0], tp->gA.mb,
+                                         (const float*)t->flow_dev_ptr[1], tp->gB.mb, 1.0f, (float*)t->flow_dev_ptr[2],
+                                         tp->gC.mb, stream);
     } else {
         rc = parsec_b200_gemm_bf16_sm100('N', 'N', rm, rn, rk, 1.0f, t->flow_dev_ptr[0], tp->gA.mb, t->flow_dev_ptr[1],
                                          tp->gB.mb, 1.0f, (float*)t->flow_dev_ptr[2], tp->gC.mb, stream);
@@ -159,7 +163,8 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
               tp->gB.P == tp->gC.P && tp->gB.Q == tp->gC.Q && tp->gA.mtype == tp->gB.mtype &&
               tp->gA.rank == tp->gC.rank && tp->gB.rank == tp->gC.rank;
     bool types = (tp->gC.mtype == PB2_MATRIX_DOUBLE && tp->gA.mtype == PB2_MATRIX_DOUBLE) ||
-                 (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16);
+                 (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16) ||
+                 (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_FLOAT);  // fp32 tiles: TF32 tensor cores
     if (!ok || !types) {
         delete tp;
         return nullptr;

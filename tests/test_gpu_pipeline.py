@@ -107,6 +107,17 @@ def test_single_tile_and_window():
         dev.close()
 
 
+def test_sorted_pending_list_keeps_parity():
+    """device_cuda_sort_pending_tasks: reordering the pending list must change neither values, counts nor versions."""
+    nb = 128
+    dev = H.Device(0, memory_block_size=nb * nb * 8, memory_number_of_blocks=60, max_inflight_tasks=4, sort_pending_tasks=1)
+    try:
+        st, cnt, ver, versions, norm, mats = _run_tiled(768, 768, 768, nb, dev)
+        assert norm < 10 and st["nb_gemm"] == cnt.gemm == 6 ** 3 and np.array_equal(versions, ver)
+    finally:
+        dev.close()
+
+
 def test_out_of_core_eviction_and_writeback():
     """HBM smaller than the working set: clean tiles are evicted, dirty C tiles are really written back (the
     reference's W2R copies nothing) and the result still matches the oracle."""

@@ -69,3 +69,34 @@ def test_mismatched_types_are_rejected():
     assert not H.lib().pb2_gemm_taskpool_new(a.h, a.h, c.h, None)
     a.close()
     c.close()
+
+
+def test_tiled_fp32_gemm_runs_on_tf32_tensor_cores():
+    """fp32 A, B, C tiles (PARSEC_MATRIX_FLOAT) go through the kind::tf32 body: the operands lose their low 13 mantissa
+    bits in the tensor core, so the bound is 2 * 2^-10 per product, i.e. ||C - Cref||inf <= 2^-9 ||A||inf ||B||inf."""
+    import torch
+    N, NB = 512, 128
+    dev = H.Device(0, memory_number_of_blocks=1024)
+    try:
+        mats, bufs = [], []
+        for seed in (1789, 1805, 1901):
+            m = H.Matrix(H.MATRIX_FLOAT, N, N, NB, NB)
+            b = torch.zeros(m.nbytes, dtype=torch.uint8).pin_memory()
+            m.set_buffer(b)
+            m.fill_lcg(seed, dev)
+            mats.append(m)
+            bufs.append(b)
+        d = O.square(N, NB)
+        hA, hB, hC = (O.tiled_to_dense(d, O.fill(d, s)) for s in (1789, 1805, 1901))
+        st = H.tiled_gemm(mats[0], mats[1], mats[2], dev)
+        assert st["nb_gemm"] == (N // NB) ** 3
+        got = O.tiled_to_dense(d, bufs[2].numpy().view(np.float32).astype(np.float64))
+        want = hC + hA @ hB
+        inf = lambda X: np.abs(X).sum(axis=1).max()
+        r = inf(got - want) / (inf(hA) * inf(hB))
+        assert r < 2.0 ** -9, r
+        assert r > 2.0 ** -24      # it really was TF32, not an fp32 FMA path
+        for m in mats:
+            m.close()
+    finally:
+        dev.close()
