@@ -296,6 +296,25 @@ int pb2_gemm_taskpool_set_comm(pb2_taskpool_t* tp, pb2_comm_t* comm);
 int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats);
 void pb2_gemm_taskpool_free(pb2_taskpool_t* tp);
 
+/* ------------------------------------------------------------------------------------------------
+ * DTD front-end: the second caller of the same device boundary (GPU tasks only).
+ * parsec_dtd_taskpool_new + parsec_context_add_taskpool/start; parsec_dtd_insert_task_with_task_class
+ * (parsec/interfaces/dtd/insert_function.c) with parsec_dtd_gpu_task_submit (:2359-2406);
+ * parsec_dtd_data_flush_all + parsec_dtd_taskpool_wait + parsec_context_wait.
+ * Dependencies are inferred from the insertion order and the access modes of the data each task touches.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_dtd_taskpool_s pb2_dtd_taskpool_t;
+pb2_dtd_taskpool_t* pb2_dtd_taskpool_new(pb2_device_t* dev);
+/* access[i]: PB2_FLOW_ACCESS_READ / _WRITE / _RW (PARSEC_INPUT / OUTPUT / INOUT); pushout_mask bit i: PARSEC_PUSHOUT on
+ * flow i (insert_function.h:70); locals: the PARSEC_VALUE arguments (at most 8) copied into pb2_gpu_task_t.locals */
+int pb2_dtd_insert_task(pb2_dtd_taskpool_t* tp, pb2_submit_fn gpu_body, int priority, int nb_flows,
+                        pb2_data_t* const* data, const uint8_t* access, int32_t pushout_mask, const int64_t* locals,
+                        int nb_locals);
+int pb2_dtd_taskpool_wait(pb2_dtd_taskpool_t* tp, int64_t* nb_executed);
+void pb2_dtd_taskpool_free(pb2_dtd_taskpool_t* tp);
+/* gemm_kernel_cuda of tests/dsl/dtd/dtd_test_simple_gemm.c:165-216: flows (A, B, C), locals (m, n, k, mb, nb, kb) */
+int pb2_dtd_gemm_body(pb2_device_t* dev, pb2_gpu_task_t* task, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
