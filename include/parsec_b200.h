@@ -105,6 +105,15 @@ int pb2_data_copy_readers(const pb2_data_t* data, int device_index);
 int pb2_data_owner_device(const pb2_data_t* data);
 void* pb2_data_copy_ptr(const pb2_data_t* data, int device_index); /* PARSEC_DATA_COPY_GET_PTR */
 
+/* The ownership / coherency state machine on bare copies (no device needed): parsec_data_copy_attach / _detach and
+ * parsec_data_start / end_transfer_ownership_to_copy (parsec/data.c:163-202, :299-433).  A CPU test replays operation
+ * sequences recorded from the reference's own data.c through these (tests/golden/ownership_trace.json). */
+int pb2_data_test_attach(pb2_data_t* data, int device_index);
+int pb2_data_test_detach(pb2_data_t* data, int device_index);
+int pb2_data_test_start_transfer(pb2_data_t* data, int device_index, int access); /* source device or -1 */
+void pb2_data_test_end_transfer(pb2_data_t* data, int device_index, int access);
+void pb2_data_test_set(pb2_data_t* data, int device_index, int coherency, int version, int readers); /* -1 = keep */
+
 /* ------------------------------------------------------------------------------------------------
  * Device module (piece 1): replaces parsec/mca/device/cuda/device_cuda_module.c and device_cuda_component.c.
  * ---------------------------------------------------------------------------------------------- */

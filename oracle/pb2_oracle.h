@@ -9,11 +9,14 @@
  * follows (relative to /root/reference) is cited next to it in pb2_oracle.c.
  *
  * Parity pinning (see DESIGN.md "Oracle"):
- *   - zone allocator: pinned against the reference's own parsec/utils/zone_malloc.c compiled from
- *     where it lies into oracle/_ref/ (tests/test_oracle_ref.py, golden tests/golden/zone_trace.json);
- *   - block-cyclic mapping, input generator, coherency/version state machine: pinned against the
- *     reference's golden values recorded in SURVEY.md (task counts 512+64+64 at N=2048/NB=256, final
- *     C-tile version == KT) and the worked sequence of SURVEY.md Appendix C;
+ *   - zone allocator, process grid and the ownership / coherency state machine: pinned against the reference's OWN
+ *     code -- parsec/utils/zone_malloc.c, parsec/data_dist/matrix/grid_2Dcyclic.c and parsec/data.c (+ class files)
+ *     compiled from where they lie into oracle/_ref/ (oracle/Makefile target ref) -- through the golden vectors
+ *     tests/golden/{zone_trace,grid,ownership_trace}.json (tests/golden/make_golden.py) and live fuzzing;
+ *   - task counts, final versions and the per-task version sequence: pinned against the values the reference
+ *     runtime produced in the survey's probe run (512+64+64 tasks at N=2048/NB=256, final C-tile version == KT)
+ *     and the worked sequence of SURVEY.md Appendix C; block-cyclic mapping and the input generator are
+ *     restatements checked by independent re-derivations in tests/test_oracle.py;
  *   - tile GEMM arithmetic: the reference ships no GEMM (its bodies call cuBLAS / an un-vendored
  *     CBLAS), so the arithmetic is "parity unpinned" at the BLAS boundary; the oracle follows the
  *     column-major convention of every CUDA body in the tree.

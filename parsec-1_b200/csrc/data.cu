@@ -217,3 +217,36 @@ extern "C" void* pb2_data_copy_ptr(const pb2_data_t* data, int dev) {
     const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
     return c ? c->device_private : nullptr;
 }
+
+// ------------------------------------------------------------------------------------------ state-machine hooks
+// parsec_data_copy_attach / _detach, parsec_data_start_transfer_ownership_to_copy, parsec_data_end_transfer_...
+// (parsec/data.c:163-202, :299-433) on bare copies, without a device: lets a CPU test drive the product's coherency
+// state machine with the operation sequences recorded from the reference's own data.c (tests/golden/ownership_trace.json).
+extern "C" int pb2_data_test_attach(pb2_data_t* data, int dev) {
+    if (!data || dev < 1 || dev >= PB2_MAX_DEVICES || data->device_copies[dev]) return PB2_ERR_BAD_PARAM;
+    pb2_copy_t* c = new pb2_copy_t();
+    c->device_index = (int8_t)dev;
+    c->original = data;
+    c->coherency_state = PB2_DATA_COHERENCY_INVALID;
+    data->device_copies[dev] = c;
+    return PB2_SUCCESS;
+}
+extern "C" int pb2_data_test_detach(pb2_data_t* data, int dev) {
+    if (!data || dev < 1 || dev >= PB2_MAX_DEVICES || !data->device_copies[dev]) return PB2_ERR_NOT_FOUND;
+    delete data->device_copies[dev];
+    data->device_copies[dev] = nullptr;
+    return PB2_SUCCESS;
+}
+extern "C" int pb2_data_test_start_transfer(pb2_data_t* data, int dev, int access) {
+    return pb2::data_start_transfer_ownership(data, dev, (uint8_t)access);
+}
+extern "C" void pb2_data_test_end_transfer(pb2_data_t* data, int dev, int access) {
+    pb2::data_end_transfer_ownership(data, dev, (uint8_t)access);
+}
+extern "C" void pb2_data_test_set(pb2_data_t* data, int dev, int coherency, int version, int readers) {
+    pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
+    if (!c) return;
+    if (coherency >= 0) c->coherency_state = (uint8_t)coherency;
+    if (version >= 0) c->version = (uint32_t)version;
+    if (readers >= 0) c->readers = readers;
+}

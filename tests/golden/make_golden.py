@@ -75,3 +75,89 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# ownership_trace.json: random operation sequences driven through the REFERENCE's parsec/data.c (attach / detach a
+# device copy, start / end of an ownership transfer, and the field updates the device module makes around them:
+# version bump, version overwrite, epilog, complete hook, reader release); the full data state after every step.
+def ownership_cases():
+    ref.ref_data_new.restype = C.c_void_p
+    ref.ref_data_new.argtypes = [C.c_uint64]
+    for name in ("ref_copy_attach_new", "ref_copy_detach", "ref_start_transfer", "ref_data_owner"):
+        getattr(ref, name).argtypes = [C.c_void_p] + [C.c_int] * {"ref_copy_attach_new": 1, "ref_copy_detach": 1,
+                                                                   "ref_start_transfer": 2, "ref_data_owner": 0}[name]
+    ref.ref_end_transfer.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    ref.ref_end_transfer.restype = None
+    ref.ref_copy_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+    ref.ref_copy_state.restype = None
+    ref.ref_copy_set.argtypes = [C.c_void_p] + [C.c_int] * 4
+    ref.ref_copy_set.restype = None
+    READ, WRITE = 4, 8
+    DEVS = (0, 2, 3)
+
+    def snapshot(d):
+        out = [int(C.c_int8(ref.ref_data_owner(d)).value)]
+        buf = (C.c_int * 4)()
+        for dev in DEVS:
+            ref.ref_copy_state(d, dev, buf)
+            out.append(list(buf))
+        return out
+
+    cases = []
+    for seed in range(24):
+        rng = random.Random(1000 + seed)
+        d = ref.ref_data_new(seed)
+        steps, pending = [], []       # pending: (dev, access) transfers started and not yet ended
+        for _ in range(150):
+            st = snapshot(d)
+            present = [dev for dev, s in zip(DEVS, st[1:]) if s[0]]
+            gpus_absent = [dev for dev in (2, 3) if dev not in present]
+            roll = rng.random()
+            if gpus_absent and roll < 0.15:
+                dev = rng.choice(gpus_absent)
+                ref.ref_copy_attach_new(d, dev)
+                op = ["attach", dev]
+            elif pending and roll < 0.45:
+                dev, access = pending.pop(rng.randrange(len(pending)))
+                ref.ref_end_transfer(d, dev, access)
+                op = ["end", dev, access]
+            elif roll < 0.75:
+                # a writer must own or be about to own: only start a WRITE where no other copy is OWNED by someone else
+                dev = rng.choice(present)
+                access = rng.choice([READ, READ, READ | WRITE, WRITE])
+                owned_elsewhere = any(s[0] and s[1] == 1 and dv != dev for dv, s in zip(DEVS, st[1:]))
+                if (access & WRITE) and owned_elsewhere:
+                    access = READ
+                r = ref.ref_start_transfer(d, dev, access)
+                pending.append((dev, access))
+                op = ["start", dev, access, r]
+            elif roll < 0.9:
+                dev = rng.choice(present)
+                cur = st[1 + DEVS.index(dev)]
+                kind = rng.choice(["version++", "version=host", "release_reader", "shared"])
+                if kind == "version++":
+                    ref.ref_copy_set(d, dev, -1, cur[3] + 1, -1)
+                elif kind == "version=host":
+                    ref.ref_copy_set(d, dev, -1, st[1][3], -1)
+                elif kind == "release_reader":
+                    ref.ref_copy_set(d, dev, -1, -1, max(0, cur[2] - 1))
+                else:
+                    ref.ref_copy_set(d, dev, 4, -1, -1)
+                op = ["set", dev, kind]
+            else:
+                idle = [dev for dev in (2, 3) if dev in present and st[1 + DEVS.index(dev)][2] == 0
+                        and not any(p[0] == dev for p in pending) and st[0] != dev]
+                if not idle:
+                    continue
+                dev = rng.choice(idle)
+                ref.ref_copy_detach(d, dev)
+                op = ["detach", dev]
+            steps.append({"op": op, "state": snapshot(d)})
+        cases.append({"seed": seed, "steps": steps})
+    json.dump(cases, open(os.path.join(HERE, "ownership_trace.json"), "w"))
+    print("wrote ownership_trace.json (%d cases, %d steps)" % (len(cases), sum(len(c["steps"]) for c in cases)))
+
+
+if __name__ == "__main__":
+    ownership_cases()
