@@ -17,7 +17,7 @@ void parsec_debug_verbose(int level, int output_id, const char* fmt, ...) { (voi
 void parsec_warning(const char* fmt, ...) { (void)fmt; }
 int parsec_mca_device_registration_completed(parsec_context_t* ctx) { (void)ctx; return 1; }
 parsec_device_module_t* parsec_mca_device_get(uint32_t idx) { (void)idx; return NULL; }
-void parsec_arena_release(parsec_data_copy_t* copy) { (void)copy; }
+void parsec_fatal(const char* fmt, ...) { fprintf(stderr, "parsec_fatal: %s\n", fmt); abort(); }
 
 /* --- accessors ------------------------------------------------------------------------------------------ */
 static char fake_dc[4096]; /* parsec_data_create only reads dc->default_dtt */
@@ -64,4 +64,56 @@ void ref_copy_set(void* data, int device, int coherency, int version, int reader
     if (coherency >= 0) c->coherency_state = (parsec_data_coherency_t)coherency;
     if (version >= 0) c->version = (uint32_t)version;
     if (readers >= 0) c->readers = readers;
+}
+
+/* --- more of the runtime, needed once arena.c / parsec_hash_table.c / the matrix collection are compiled in ---- */
+#include <stdbool.h>
+static void* glue_alloc(size_t size) { return malloc(size); }
+static void glue_free(void* p) { free(p); }
+parsec_data_allocate_t parsec_data_allocate = glue_alloc; /* function-pointer globals of the runtime (runtime.h:100-101) */
+parsec_data_free_t parsec_data_free = glue_free;
+int parsec_mca_param_reg_int_name(const char* type, const char* name, const char* help, bool internal, bool read_only,
+                                  int default_value, int* current_value) {
+    (void)type; (void)name; (void)help; (void)internal; (void)read_only;
+    if (current_value) *current_value = default_value;
+    return 0;
+}
+int parsec_mca_param_lookup_int(int index, int* value) { (void)index; (void)value; return -1; }
+
+/* --- the reference's 2D block-cyclic collection, driven through its own vtable ------------------------------ */
+#include "parsec/data_dist/matrix/two_dim_rectangle_cyclic.h"
+
+void* ref_bc_new(int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q, int kp, int kq,
+                 int ip, int jq) {
+    parsec_matrix_block_cyclic_t* dc = (parsec_matrix_block_cyclic_t*)calloc(1, sizeof(*dc));
+    parsec_matrix_block_cyclic_init(dc, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_TILE, myrank, mb, nb, lm, ln, i, j, m, n, P, Q,
+                                    kp, kq, ip, jq);
+    return dc;
+}
+/* out: mt, nt, lmt, lnt, lm, ln, llm, lln, bsiz, nb_elem_r, nb_elem_c, nb_local_tiles, rrank, crank */
+void ref_bc_geometry(void* p, int* out) {
+    parsec_matrix_block_cyclic_t* dc = (parsec_matrix_block_cyclic_t*)p;
+    int v[14] = {dc->super.mt, dc->super.nt, dc->super.lmt, dc->super.lnt, dc->super.lm, dc->super.ln, dc->super.llm,
+                 dc->super.lln, dc->super.bsiz, dc->nb_elem_r, dc->nb_elem_c, dc->super.nb_local_tiles, dc->grid.rrank,
+                 dc->grid.crank};
+    memcpy(out, v, sizeof(v));
+}
+int ref_bc_rank_of(void* p, int m, int n) {
+    parsec_data_collection_t* dc = (parsec_data_collection_t*)p;
+    return (int)dc->rank_of(dc, m, n);
+}
+uint64_t ref_bc_data_key(void* p, int m, int n) {
+    parsec_data_collection_t* dc = (parsec_data_collection_t*)p;
+    return dc->data_key(dc, m, n);
+}
+/* byte offset of tile (m, n) inside the local matrix, its parsec_data_t key and nb_elts, through the real data_of */
+int64_t ref_bc_tile_offset(void* p, int m, int n, uint64_t* key, uint32_t* nb_elts) {
+    parsec_matrix_block_cyclic_t* bc = (parsec_matrix_block_cyclic_t*)p;
+    parsec_data_collection_t* dc = (parsec_data_collection_t*)p;
+    static char base[1]; /* symbolic: data_of only does pointer arithmetic on dc->mat */
+    if (!bc->mat) bc->mat = base;
+    parsec_data_t* d = dc->data_of(dc, m, n);
+    if (key) *key = d->key;
+    if (nb_elts) *nb_elts = d->nb_elts;
+    return (int64_t)((char*)d->device_copies[0]->device_private - (char*)bc->mat);
 }

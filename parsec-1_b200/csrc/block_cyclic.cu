@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "pb2_internal.h"
 #include "pb2_types.h"
 
@@ -184,7 +186,9 @@ extern "C" int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed,
         for (int m = 0; m < dc->mt; ++m)
             if (pb2_matrix_rank_of(dc, m, n) == dc->myrank) coords[(size_t)pb2_matrix_position(dc, m, n)] = make_int2(m, n);
     const size_t tile_bytes = (size_t)dc->bsiz * dc->elem_size;
-    const int batch = (int)std::max<size_t>(1, std::min<size_t>((size_t)dc->nb_local_tiles, (256u << 20) / tile_bytes));
+    // at most 256 MiB of staging and 65535 tiles (gridDim.y) per launch
+    const int batch = (int)std::max<size_t>(
+        1, std::min<size_t>({(size_t)dc->nb_local_tiles, (size_t)(256u << 20) / tile_bytes, (size_t)65535}));
     char* dbuf = nullptr;
     int2* dcoords = nullptr;
     if (cudaMalloc((void**)&dbuf, tile_bytes * batch) != cudaSuccess) return PB2_ERR_OUT_OF_RESOURCE;
@@ -204,7 +208,8 @@ extern "C" int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed,
             lcg_fill_tiles<float><<<grid, 128>>>((float*)dbuf, dcoords + t0, dc->mb, dc->nb, dc->m, seed);
         else
             lcg_fill_tiles<__nv_bfloat16><<<grid, 128>>>((__nv_bfloat16*)dbuf, dcoords + t0, dc->mb, dc->nb, dc->m, seed);
-        if (cudaMemcpy((char*)dc->mat + (size_t)t0 * tile_bytes, dbuf, tile_bytes * nt, cudaMemcpyDeviceToHost) != cudaSuccess)
+        if (cudaGetLastError() != cudaSuccess ||
+            cudaMemcpy((char*)dc->mat + (size_t)t0 * tile_bytes, dbuf, tile_bytes * nt, cudaMemcpyDeviceToHost) != cudaSuccess)
             rc = PB2_ERR_DEVICE;
     }
     cudaFree(dbuf);
@@ -289,7 +294,7 @@ extern "C" int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsign
     void* scratch = nullptr;
     int rc = fill_scratch_address(cuda_index, &scratch);
     if (rc != PB2_SUCCESS) return rc;
-    const long long batch = (long long)(PB2_FILL_SCRATCH_BYTES / tile_bytes);
+    const long long batch = std::min<long long>((long long)(PB2_FILL_SCRATCH_BYTES / tile_bytes), 65535);  // gridDim.y
     for (long long t0 = 0; t0 < dc->nb_local_tiles; t0 += batch) {
         const int nt = (int)std::min<long long>(batch, dc->nb_local_tiles - t0);
         dim3 grid((dc->nb + 127) / 128, nt);

@@ -161,3 +161,62 @@ def ownership_cases():
 
 if __name__ == "__main__":
     ownership_cases()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# block_cyclic.json: parsec_matrix_block_cyclic_init + rank_of / data_key / data_of of the REFERENCE's
+# two_dim_rectangle_cyclic.c, for every tile of a few (matrix, tiling, grid, rank) combinations.
+def block_cyclic_cases():
+    ref.ref_bc_new.restype = C.c_void_p
+    ref.ref_bc_new.argtypes = [C.c_int] * 15
+    ref.ref_bc_geometry.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    ref.ref_bc_rank_of.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    ref.ref_bc_data_key.restype = C.c_uint64
+    ref.ref_bc_data_key.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    ref.ref_bc_tile_offset.restype = C.c_int64
+    ref.ref_bc_tile_offset.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+    cases = []
+    for (M, N, mb, nb) in [(2048, 2048, 256, 256), (1000, 1000, 96, 96), (250, 130, 40, 40), (640, 384, 64, 128)]:
+        for (P, Q) in [(1, 1), (1, 2), (2, 2), (2, 4), (3, 2)]:
+            for rank in range(P * Q):
+                dc = ref.ref_bc_new(rank, mb, nb, M, N, 0, 0, M, N, P, Q, 1, 1, 0, 0)
+                g = (C.c_int * 14)()
+                ref.ref_bc_geometry(dc, g)
+                geo = dict(zip("mt nt lmt lnt lm ln llm lln bsiz nb_elem_r nb_elem_c nb_local_tiles rrank crank".split(), list(g)))
+                tiles = []
+                for n in range(geo["nt"]):
+                    for m in range(geo["mt"]):
+                        owner = ref.ref_bc_rank_of(dc, m, n)
+                        entry = [m, n, owner, int(ref.ref_bc_data_key(dc, m, n))]
+                        if owner == rank:
+                            key, nbe = C.c_uint64(), C.c_uint32()
+                            off = ref.ref_bc_tile_offset(dc, m, n, C.byref(key), C.byref(nbe))
+                            entry += [int(off), int(key.value), int(nbe.value)]
+                        tiles.append(entry)
+                cases.append({"M": M, "N": N, "mb": mb, "nb": nb, "P": P, "Q": Q, "rank": rank, "geo": geo, "tiles": tiles})
+    json.dump(cases, open(os.path.join(HERE, "block_cyclic.json"), "w"))
+    print("wrote block_cyclic.json (%d descriptors, %d tiles)" % (len(cases), sum(len(c["tiles"]) for c in cases)))
+
+
+if __name__ == "__main__":
+    block_cyclic_cases()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# lcg_tiles.json: tiles produced by the REFERENCE's own initialize_tile() (tests/dsl/dtd/dtd_test_simple_gemm.c:68-91,
+# compiled in place through oracle/refshim/gen_wrapper.c), the synthetic-input generator of the path.
+def lcg_cases():
+    ref.ref_init_tile.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_uint]
+    cases = []
+    for (m, n, mb, nb, M, seed) in [(0, 0, 8, 8, 64, 1789), (3, 5, 16, 4, 1024, 1805), (31, 31, 8, 8, 32768, 1901),
+                                    (7, 2, 5, 9, 250, 1789), (63, 63, 4, 4, 65536, 1805), (1, 0, 32, 2, 2048, 1901)]:
+        buf = (C.c_double * (mb * nb))()
+        assert ref.ref_init_tile(buf, m, n, mb, nb, M, mb, seed) == 0
+        cases.append({"m": m, "n": n, "mb": mb, "nb": nb, "M": M, "ld": mb, "seed": seed,
+                      "values": [float(v).hex() for v in buf]})
+    json.dump(cases, open(os.path.join(HERE, "lcg_tiles.json"), "w"))
+    print("wrote lcg_tiles.json (%d tiles)" % len(cases))
+
+
+if __name__ == "__main__":
+    lcg_cases()

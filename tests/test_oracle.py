@@ -249,3 +249,12 @@ def test_read_only_tiles_stay_version_zero_and_move_once():
         assert (e["kind"] == O.EV_POP).sum() == ntiles * readers
         assert e[e["kind"] == O.EV_POP]["transfer"].sum() == 0
     assert (ev["kind"] == O.EV_COMPLETE).sum() == 3 * 2 * 4
+
+
+def test_generator_matches_reference_initialize_tile_golden():
+    """tests/golden/lcg_tiles.json was written by the reference's own initialize_tile() compiled in place."""
+    for c in json.load(open(os.path.join(HERE, "golden", "lcg_tiles.json"))):
+        tile = np.empty(c["mb"] * c["nb"])
+        O.lib().orc_init_tile(tile.ctypes.data, c["m"], c["n"], c["mb"], c["nb"], c["M"], c["ld"], c["seed"])
+        want = np.array([float.fromhex(v) for v in c["values"]])
+        assert np.array_equal(tile, want), c
