@@ -142,7 +142,8 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=4096, help="matrix order of the bounded CPU sample")
     ap.add_argument("--window", type=int, default=0, help="C-tile chains in flight (0 = all)")
     ap.add_argument("--inflight", type=int, default=256)
-    ap.add_argument("--streams", type=int, default=6)
+    ap.add_argument("--streams", type=int, default=18, help="h2d + d2h + exec streams (the module spreads a task over as "
+                    "many exec streams as its tile size needs: 5 at NB=1024, 16 at NB=512)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--hbm-gib", type=float, default=0.0,
                     help="cap the HBM tile heap (GiB) to run out of core: the BASELINE configs[3] mechanism (LRU evict + "
@@ -290,7 +291,8 @@ def main():
                                 "(BASELINE configs[2] shape; weak scaling from N=%d)" % (N, NB, P, Q, world, args.n)),
                    "tasks_per_step": (N // NB) ** 3, "host_cores": os.cpu_count(), "replicas_diagnostic": bool(args.replicas),
                    "l2": "inputs (%.1f GiB) far larger than L2" % (N * N * (8 if bf16 else 24) / 2 ** 30),
-                   "parallelism": "1 process per GPU, %dx%d grid; %d exec streams per GPU" % (P, Q, args.streams - 2),
+                   "parallelism": "1 process per GPU, %dx%d grid; %s exec streams in use per GPU" % (
+                       P, Q, prof["resident_launches"] if prof else "?"),
                    "pct_of_tensor_peak": 100.0 * value / world / (peak_tf * 1e3)},
         "e2e": {"value": e2e, "unit": "GFLOP/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": st_e2e["data_in_from_host"] // max(1, args.steps),

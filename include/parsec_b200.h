@@ -121,7 +121,8 @@ typedef struct pb2_device_params_s {
     int memory_use_percent;       /* device_cuda_memory_use (95)            device_cuda_component.c:187 */
     int64_t memory_block_size;    /* device_cuda_memory_block_size (512 KiB) :183 */
     int64_t memory_number_of_blocks; /* device_cuda_memory_number_of_blocks (-1 = from percent) :191 */
-    int max_streams;              /* device_cuda_max_streams (6: h2d + d2h + 4 exec) :199 */
+    int max_streams;              /* device_cuda_max_streams :199 (reference default 6 = h2d + d2h + 4 exec; default here 18:
+                                     a task is spread over as many exec streams as its tile size needs, 4..16) */
     int max_number_of_ejected_data; /* device_cuda_max_number_of_ejected_data (20) :195 */
     int max_inflight_tasks;       /* tasks enqueued on the GPU but not completed (reference: 4 per stream, device_gpu.h:22) */
     int trace_events;             /* record pb2_event_t for every data-state transition */

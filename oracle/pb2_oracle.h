@@ -9,14 +9,15 @@
  * follows (relative to /root/reference) is cited next to it in pb2_oracle.c.
  *
  * Parity pinning (see DESIGN.md "Oracle"):
- *   - zone allocator, process grid and the ownership / coherency state machine: pinned against the reference's OWN
- *     code -- parsec/utils/zone_malloc.c, parsec/data_dist/matrix/grid_2Dcyclic.c and parsec/data.c (+ class files)
- *     compiled from where they lie into oracle/_ref/ (oracle/Makefile target ref) -- through the golden vectors
- *     tests/golden/{zone_trace,grid,ownership_trace}.json (tests/golden/make_golden.py) and live fuzzing;
+ *   - zone allocator, process grid, ownership / coherency state machine, block-cyclic collection and the input
+ *     generator: pinned against the reference's OWN code -- parsec/utils/zone_malloc.c, grid_2Dcyclic.c, parsec/data.c,
+ *     two_dim_rectangle_cyclic.c + matrix.c and initialize_tile() of tests/dsl/dtd/dtd_test_simple_gemm.c, compiled
+ *     from where they lie into oracle/_ref/ (oracle/Makefile target ref) -- through the golden vectors
+ *     tests/golden/{zone_trace,grid,ownership_trace,block_cyclic,lcg_tiles}.json (tests/golden/make_golden.py)
+ *     and live fuzzing;
  *   - task counts, final versions and the per-task version sequence: pinned against the values the reference
  *     runtime produced in the survey's probe run (512+64+64 tasks at N=2048/NB=256, final C-tile version == KT)
- *     and the worked sequence of SURVEY.md Appendix C; block-cyclic mapping and the input generator are
- *     restatements checked by independent re-derivations in tests/test_oracle.py;
+ *     and the worked sequence of SURVEY.md Appendix C;
  *   - tile GEMM arithmetic: the reference ships no GEMM (its bodies call cuBLAS / an un-vendored
  *     CBLAS), so the arithmetic is "parity unpinned" at the BLAS boundary; the oracle follows the
  *     column-major convention of every CUDA body in the tree.

@@ -72,6 +72,7 @@ struct pb2_device_s {
     std::vector<cudaStream_t> exec;
     std::vector<uint64_t> exec_waited_seq;
     int next_exec = 0;
+    int active_exec = 0;  // exec streams the last task was spread over (see try_submit)
     uint64_t h2d_seq = 0;  // number of push events recorded so far
     cudaEvent_t h2d_events[pb2::EVENT_RING];
     std::vector<cudaEvent_t> event_pool;
@@ -101,7 +102,7 @@ extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->memory_use_percent = 95;
     p->memory_block_size = 512 * 1024;
     p->memory_number_of_blocks = -1;
-    p->max_streams = 6;
+    p->max_streams = 18;  // h2d + d2h + up to 16 exec (the reference's default is 6; small tiles need the concurrency)
     p->max_number_of_ejected_data = PB2_MAX_PARAM_COUNT;
     p->max_inflight_tasks = 256;
     p->trace_events = 0;
@@ -299,7 +300,7 @@ extern "C" int64_t pb2_device_get_events(pb2_device_t* d, pb2_event_t* out, int6
 
 extern "C" int64_t pb2_device_get_launch_ms(pb2_device_t* d, float* out, int64_t max_samples, int* nb_exec_streams) {
     if (!d) return PB2_ERR_BAD_PARAM;
-    if (nb_exec_streams) *nb_exec_streams = (int)d->exec.size();
+    if (nb_exec_streams) *nb_exec_streams = d->active_exec > 0 ? d->active_exec : (int)d->exec.size();
     cudaSetDevice(d->cuda_index);
     int64_t n = 0;
     for (auto& marks : d->launch_marks) {
@@ -563,8 +564,17 @@ static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
 
     cudaStream_t last = d->h2d;
     if (t->task_type == 0 && t->submit) {
-        int s = d->next_exec;
-        d->next_exec = (d->next_exec + 1) % (int)d->exec.size();
+        // How many exec streams to spread over: a tile kernel has about one CTA per 128 KiB of its written tile
+        // (128x128 fp64 or 128x256 fp32), and a B200 wants ~2 x 148 CTAs queued.  An NB=1024 fp64 task (64 CTAs) uses 5
+        // streams, an NB=512 one (16 CTAs) all 16, an NB=2048 one (256 CTAs) the minimum of 4.
+        size_t wbytes = 0;
+        for (int i = 0; i < t->nb_flows; ++i)
+            if (t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) wbytes = std::max<size_t>(wbytes, t->flow_nb_elts[i]);
+        const int ctas = (int)std::max<size_t>(1, wbytes >> 17);
+        const int active = std::min<int>((int)d->exec.size(), std::max(4, (2 * 148 + ctas - 1) / ctas));
+        d->active_exec = active;
+        int s = d->next_exec % active;
+        d->next_exec = (d->next_exec + 1) % active;
         st->exec_stream = s;
         if (need_seq > d->exec_waited_seq[s]) {
             // waiting on a newer event of the same in-order stream covers every older one; if the ring has
