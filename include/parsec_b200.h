@@ -216,6 +216,18 @@ int pb2_kernel_scheduler(pb2_device_t* dev, pb2_gpu_task_t* task);
  * drains.  Same mutex protocol as device_cuda_module.c:2573-2589 / :2742-2753, split in two calls. */
 int pb2_device_hold(pb2_device_t* dev);
 int pb2_device_manage(pb2_device_t* dev);
+/* Per-stream scratch for task bodies: parsec_gpu_pop_workspace / parsec_gpu_push_workspace /
+ * parsec_gpu_free_workspace (parsec/mca/device/device_gpu.c:168-246).  To be called from a submit callback with the
+ * cuda_stream it was handed.  The first pop on a stream carves PB2_GPU_MAX_WORKSPACE buffers of `size` bytes from the
+ * HBM heap (evicting clean tiles if it must) and keeps them until pb2_device_free_workspace; a pop takes the top of
+ * that stream's stack, a push gives the last one back.  Work queued on one stream runs in order, which is what makes a
+ * buffer handed back right after the launch safe to hand to the next body on the same stream.  Returns NULL when the
+ * stream is not one of the device's exec streams, the stack is empty, `size` exceeds the size of the first pop, or the
+ * heap has no room. */
+#define PB2_GPU_MAX_WORKSPACE 2
+void* pb2_device_pop_workspace(pb2_device_t* dev, void* cuda_stream, size_t size);
+int pb2_device_push_workspace(pb2_device_t* dev, void* cuda_stream);
+int pb2_device_free_workspace(pb2_device_t* dev);
 /* parsec_default_cuda_stage_in / _stage_out (device_cuda_module.c:1179-1209, :1220-1250) */
 int pb2_default_stage_in(pb2_gpu_task_t* task, uint32_t flow_mask, void* cuda_stream);
 int pb2_default_stage_out(pb2_gpu_task_t* task, uint32_t flow_mask, void* cuda_stream);

@@ -87,8 +87,14 @@ struct pb2_device_s {
     pb2::CopyList* lists[3] = {nullptr, &lru, &owned_lru};
     pb2_device_stats_t stats;
     std::vector<pb2_event_t> events;
-    std::mutex events_lock;
     bool failed = false;
+    struct Workspace {  // parsec_gpu_workspace_t (device_gpu.h:155-159), one per exec stream
+        void* buf[PB2_GPU_MAX_WORKSPACE] = {nullptr};
+        int stack_head = -1;
+        size_t size = 0;
+        bool ready = false;
+    };
+    std::vector<Workspace> workspace;
     std::unordered_map<void*, size_t> registered;
     std::vector<std::vector<cudaEvent_t>> launch_marks;  // profile_launches: completion marks per exec stream
 };
@@ -223,6 +229,7 @@ extern "C" int pb2_device_destroy(pb2_device_t* d) {
     cudaDeviceSynchronize();
     while (pb2_copy_t* c = d->lru.pop_front()) release_copy(d, c);
     while (pb2_copy_t* c = d->owned_lru.pop_front()) release_copy(d, c);
+    pb2_device_free_workspace(d);
     for (auto& kv : d->registered) cudaHostUnregister(kv.first);
     for (cudaStream_t s : d->exec) cudaStreamDestroy(s);
     cudaStreamDestroy(d->h2d);
@@ -990,3 +997,62 @@ extern "C" int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data) {
 }
 
 extern "C" int pb2_device_exec_streams(pb2_device_t* d) { return d ? (int)d->exec.size() : 0; }
+
+// ------------------------------------------------------------------------------------ per-stream workspace (a19)
+// parsec_gpu_pop_workspace / _push_workspace / _free_workspace (device_gpu.c:168-246).  Manager thread only (the
+// submit callback runs there), like every other user of the HBM heap.
+static int exec_stream_index(pb2_device_s* d, void* cuda_stream) {
+    for (size_t i = 0; i < d->exec.size(); ++i)
+        if ((void*)d->exec[i] == cuda_stream) return (int)i;
+    return -1;
+}
+
+extern "C" void* pb2_device_pop_workspace(pb2_device_t* d, void* cuda_stream, size_t size) {
+    if (!d || !size) return nullptr;
+    const int s = exec_stream_index(d, cuda_stream);
+    if (s < 0) return nullptr;
+    if (d->workspace.size() != d->exec.size()) d->workspace.resize(d->exec.size());
+    pb2_device_s::Workspace& w = d->workspace[s];
+    if (!w.ready) {
+        for (int i = 0; i < PB2_GPU_MAX_WORKSPACE; ++i) {
+            w.buf[i] = alloc_evicting(d, size, nullptr);
+            if (!w.buf[i]) {  // no room: give back what was taken, stay un-initialised
+                for (int j = 0; j < i; ++j) {
+                    d->heap->free(w.buf[j]);
+                    w.buf[j] = nullptr;
+                }
+                return nullptr;
+            }
+        }
+        w.size = size;
+        w.stack_head = PB2_GPU_MAX_WORKSPACE - 1;
+        w.ready = true;
+    }
+    if (size > w.size || w.stack_head < 0) return nullptr;  // the reference asserts; this boundary reports
+    return w.buf[w.stack_head--];
+}
+
+extern "C" int pb2_device_push_workspace(pb2_device_t* d, void* cuda_stream) {
+    if (!d) return PB2_ERR_BAD_PARAM;
+    const int s = exec_stream_index(d, cuda_stream);
+    if (s < 0 || (size_t)s >= d->workspace.size() || !d->workspace[s].ready) return PB2_ERR_BAD_PARAM;
+    pb2_device_s::Workspace& w = d->workspace[s];
+    if (w.stack_head + 1 >= PB2_GPU_MAX_WORKSPACE) return PB2_ERR_BAD_PARAM;
+    w.stack_head++;
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_device_free_workspace(pb2_device_t* d) {
+    if (!d) return PB2_ERR_BAD_PARAM;
+    for (auto& w : d->workspace) {
+        if (!w.ready) continue;
+        for (int i = 0; i < PB2_GPU_MAX_WORKSPACE; ++i) {
+            if (w.buf[i]) d->heap->free(w.buf[i]);
+            w.buf[i] = nullptr;
+        }
+        w.ready = false;
+        w.stack_head = -1;
+        w.size = 0;
+    }
+    return PB2_SUCCESS;
+}

@@ -98,6 +98,8 @@ def lib():
         "pb2_device_get_launch_ms": (i64, [vp, vp, i64, C.POINTER(i32)]),
         "pb2_kernel_scheduler": (i32, [vp, vp]), "pb2_device_hold": (i32, [vp]), "pb2_device_manage": (i32, [vp]),
         "pb2_default_stage_in": (i32, [vp, u32, vp]), "pb2_default_stage_out": (i32, [vp, u32, vp]),
+        "pb2_device_pop_workspace": (vp, [vp, vp, sz]), "pb2_device_push_workspace": (i32, [vp, vp]),
+        "pb2_device_free_workspace": (i32, [vp]),
         "pb2_matrix_block_cyclic_new": (vp, [i32] * 16), "pb2_matrix_block_cyclic_free": (None, [vp]),
         "pb2_matrix_set_mat": (i32, [vp, vp]), "pb2_matrix_nb_local_tiles": (i64, [vp]),
         "pb2_matrix_mt": (i32, [vp]), "pb2_matrix_nt": (i32, [vp]), "pb2_matrix_rank_of": (i32, [vp, i32, i32]),
