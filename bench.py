@@ -140,7 +140,7 @@ def main():
     ap.add_argument("--n", type=int, default=32768, help="matrix order (BASELINE configs[1]: 32768)")
     ap.add_argument("--nb", type=int, default=1024, help="tile size")
     ap.add_argument("--cpu-n", type=int, default=4096, help="matrix order of the bounded CPU sample")
-    ap.add_argument("--window", type=int, default=0, help="C-tile chains in flight (0 = all)")
+    ap.add_argument("--window", type=int, default=0, help="C-tile chains in flight (0 = the taskpool default: 128, or 16 for tensor-core bodies)")
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=18, help="h2d + d2h + exec streams (the module spreads a task over as "
                     "many exec streams as its tile size needs: 5 at NB=1024, 16 at NB=512)")
@@ -311,7 +311,7 @@ def main():
                      "frac": (achieved_tf / peak_tf) if prof else None,
                      # dram bytes per launch from one ncu --set full capture (profiles/dgemm_tma_r1_ncu.md)
                      "traffic": None if bf16 else 25206528,
-                     "kernel": "pb2::gemm_bf16_tcgen05" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
+                     "kernel": "pb2::gemm_umma_pair" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
                      "detail": prof, "algorithmic_flops_per_launch": per_launch_flops},
     }
     if rank == 0 and not args.no_cpu_baseline:

@@ -53,7 +53,10 @@ struct pb2_taskpool_s {
     // C-tile chains in flight (0 = all).  With every chain active the DAG advances k-outer in lockstep and all C
     // tiles finish, and are written back, together at the very end; a window lets finished tiles leave (D2H) while
     // later chains compute: +4 % resident, +7 % end to end at N=32768 (measured with 64..256, B200).
-    int64_t window = 128;
+    // -1 = chosen in run(): 128 chains, or 16 when a whole chain computes in about the time its C tile takes to go
+    // back over PCIe (tensor-core bodies): there the write-back is the critical path and has to start early
+    // (bf16 N=32768 NB=2048: 658 -> 830 TFLOP/s resident), while the FP64 body wants the deeper stage-in lookahead.
+    int64_t window = -1;
     std::vector<std::pair<int, int>> chains;
     size_t next_chain = 0;
     int64_t nb_gemm = 0, nb_read_a = 0, nb_read_b = 0;
@@ -311,6 +314,12 @@ extern "C" int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats
     int rc = prepare_operands(tp);
     if (rc != PB2_SUCCESS) tp->status = rc;
     int64_t w = tp->window > 0 ? tp->window : (int64_t)tp->chains.size();
+    if (tp->window < 0) {
+        // chain time / write-back time of its C tile = 2 K pcie / (rate * sizeof(C element)), nominal rates
+        const double rate = tp->gA.mtype == PB2_MATRIX_FLOAT ? 700e12 : 1100e12;
+        const double ratio = 2.0 * (double)tp->gA.n * 50e9 / (rate * (double)tp->gC.es);
+        w = (tp->gC.mtype != PB2_MATRIX_DOUBLE && ratio < 2.0) ? 16 : 128;
+    }
     while (!tp->status && tp->next_chain < tp->chains.size() && (int64_t)tp->next_chain < w) {
         auto mn = tp->chains[tp->next_chain++];
         rc = spawn_gemm(tp, mn.first, mn.second, 0);

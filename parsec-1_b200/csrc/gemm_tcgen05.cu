@@ -18,6 +18,11 @@
 //
 // Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
 // warps 2-5 = epilogue (warp w may only touch TMEM lanes 32*(w%4) .. +31, and 2,3,4,5 cover all four quarters).
+//
+// Two kernels share these pieces: gemm_bf16_tcgen05 (one CTA per 128 x 256 tile, cta_group::1) and the default
+// gemm_umma_pair (a cluster of two CTAs per 256 x 256 tile, cta_group::2, see below).  Both finish through
+// umma_epilogue_tma (C moved by TMA boxes through the idle operand ring) or, for a C that TMA cannot address,
+// through the register epilogue.
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -39,7 +44,7 @@ constexpr int G_B_BYTES = G_BN * 128;  // 32 KiB: one box [256 n][128 bytes of k
 constexpr int G_STAGE_BYTES = G_A_BYTES + G_B_BYTES;
 constexpr int G_THREADS = 192;
 constexpr int G_TMEM_COLS = 256;
-constexpr size_t gemm_smem(int stages) { return (size_t)stages * G_STAGE_BYTES + 1024 + 256; }
+constexpr size_t gemm_smem(int stages) { return (size_t)stages * G_STAGE_BYTES + 1024 + 512; }
 
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor), built per element type in the kernel:
 //   [4,6) c_format = 1 (F32); [7,10) a_format, [10,13) b_format = 1 (BF16) or 2 (TF32);
@@ -108,12 +113,146 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
+// epilogue of one warp: TMEM -> registers -> global (column-major, 128-byte coalesced per column); `quarter` selects
+// the 32 TMEM lanes (rows of the tile) this warp may touch
+__device__ __forceinline__ void umma_epilogue(uint32_t tmem_base, int quarter, int lane, int m0, int n0, int M, int N, int KT,
+                                              float alpha, float beta, float* __restrict__ C, int ldc, uint64_t* tmem_full) {
+    const int row = m0 + quarter * 32 + lane;
+    if (beta != 0.0f && m0 + quarter * 32 < M) {
+        // pull this warp's 32-row strip of the old C tile towards L2 while the main loop runs: for one column the
+        // strip is one 128-byte line; lane j takes columns j, j+32, ...
+        const float* strip = C + (size_t)(m0 + quarter * 32);
+        for (int c = lane; c < G_BN && n0 + c < N; c += 32)
+            asm volatile("prefetch.global.L2 [%0];\n" ::"l"(strip + (size_t)(n0 + c) * ldc));
+    }
+    if (KT > 0) {
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+    }
+#pragma unroll 1
+    for (int c0 = 0; c0 < G_BN; c0 += 32) {
+        if (n0 + c0 >= N) break;  // warp-uniform
+        uint32_t v[32];
+        if (KT > 0) {
+            tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (row < M) {
+            float* base = C + (size_t)row + (size_t)(n0 + c0) * ldc;
+            const int ncols = min(32, N - (n0 + c0));
+            if (beta != 0.0f) {
+                // all 32 loads of the chunk are issued before the first use: one DRAM round trip per chunk
+                // instead of one per column
+                float old[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) old[j] = (j < ncols) ? __ldcs(base + (size_t)j * ldc) : 0.0f;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]) + beta * old[j];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]);
+            }
+        }
+    }
+}
+
+// TMA-staged epilogue (used when C is 16-byte aligned with ldc % 4 == 0).  Once the accumulator is complete the operand
+// ring is idle, so each epilogue warp turns its quarter of it into E_NBUF buffers of 32 rows x 32 columns of fp32
+// (4 KiB, one TMA box of C).  beta != 0: the boxes of the old C strip are requested up front, E_NBUF in flight, instead
+// of one dependent global-load round trip per 32 columns.  The result overwrites the box in place (each lane owns its
+// row: bank = lane) and leaves through a TMA store, which also clips ragged edges; the warp never waits on a store
+// except to recycle a buffer for columns >= 32 * E_NBUF.
+constexpr int E_NBUF = 6, E_BOX_BYTES = 32 * 32 * 4;
+constexpr int E_RING_BYTES = 4 * E_NBUF * E_BOX_BYTES;  // 96 KiB: every variant's operand ring is at least this large
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];\n" ::"l"(map),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+
+// ring: the CTA's operand ring (1024-byte aligned); cbar: 4 * E_NBUF mbarriers initialised to count 1
+__device__ __forceinline__ void umma_epilogue_tma(uint32_t tmem_base, int quarter, int lane, int m0, int n0, int M, int N,
+                                                  int KT, float alpha, float beta, const CUtensorMap* mapC, uint8_t* ring,
+                                                  uint64_t* cbar, uint64_t* tmem_full, const float* __restrict__ C, int ldc) {
+    const int row0 = m0 + quarter * 32;
+    const bool live = row0 < M && n0 < N;  // warp-uniform
+    const int nchunks = live ? (min(G_BN, N - n0) + 31) / 32 : 0;
+    const bool readc = beta != 0.0f;
+    if (live && readc) {
+        const float* strip = C + (size_t)row0;
+        for (int c = lane; c < G_BN && n0 + c < N; c += 32)
+            asm volatile("prefetch.global.L2 [%0];\n" ::"l"(strip + (size_t)(n0 + c) * ldc));
+    }
+    if (KT > 0) {
+        mbar_wait(tmem_full, 0);  // every MMA has completed: the operand ring is no longer read
+        tc_fence_after();
+    }
+    if (!live) return;
+    float* bufs = reinterpret_cast<float*>(ring + quarter * (E_NBUF * E_BOX_BYTES));
+    uint64_t* bar = cbar + quarter * E_NBUF;
+    if (readc && lane == 0) {
+        tma_prefetch_desc(mapC);
+        for (int c = 0; c < nchunks && c < E_NBUF; ++c) {
+            mbar_arrive_expect_tx(&bar[c], E_BOX_BYTES);
+            tma_load_2d(bufs + c * (E_BOX_BYTES / 4), mapC, row0, n0 + 32 * c, &bar[c]);
+        }
+    }
+#pragma unroll 1
+    for (int c = 0; c < nchunks; ++c) {
+        const int b = c % E_NBUF;
+        float* buf = bufs + b * (E_BOX_BYTES / 4);
+        uint32_t v[32];
+        if (KT > 0) {
+            tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(32 * c), v);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (readc) {
+            mbar_wait(&bar[b], (uint32_t)(c / E_NBUF) & 1u);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) buf[j * 32 + lane] = alpha * __uint_as_float(v[j]) + beta * buf[j * 32 + lane];
+        } else {
+            if (c >= E_NBUF) {  // the store that last read this buffer must be done with it
+                if (lane == 0) tma_store_wait_read<E_NBUF - 1>();
+                __syncwarp();
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) buf[j * 32 + lane] = alpha * __uint_as_float(v[j]);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(mapC, buf, row0, n0 + 32 * c);
+            tma_store_commit();
+            if (readc && c + E_NBUF < nchunks) {  // recycle this buffer for the box E_NBUF columns-chunks ahead
+                tma_store_wait_read<0>();
+                mbar_arrive_expect_tx(&bar[b], E_BOX_BYTES);
+                tma_load_2d(buf, mapC, row0, n0 + 32 * (c + E_NBUF), &bar[b]);
+            }
+        }
+    }
+    if (lane == 0) tma_store_wait_all();
+    __syncwarp();
+}
+
 // EB = operand element size: 2 = bf16 (kind::f16), 4 = fp32 consumed as TF32 (kind::tf32).  A stage is 128 bytes deep
 // along K for B (64 bf16 or 32 fp32) and always 48 KiB; an UMMA consumes 32 bytes of K (16 bf16 / 8 tf32).
 template <int G_STAGES, int EB>
 __global__ void __launch_bounds__(G_THREADS, G_STAGES <= 2 ? 2 : 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
-                  float alpha, float beta, float* __restrict__ C, int ldc) {
+                  float alpha, float beta, float* __restrict__ C, int ldc, const __grid_constant__ CUtensorMap mapC, int c_tma) {
     constexpr int BKE = 128 / EB;             // K elements per stage
     constexpr int MBOX = 128 / EB;            // m elements per A box (one 128-byte row)
     constexpr int NBOX = G_BM / MBOX;         // A boxes per stage
@@ -130,6 +269,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     uint64_t* empty = full + G_STAGES;
     uint64_t* tmem_full = empty + G_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    uint64_t* cbar = tmem_full + 2;  // 4 warps x E_NBUF barriers of the TMA-staged epilogue
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_m = (M + G_BM - 1) / G_BM;
@@ -142,6 +282,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             mbar_init(&empty[s], 1);
         }
         mbar_init(tmem_full, 1);
+        for (int i = 0; i < 4 * E_NBUF; ++i) mbar_init(&cbar[i], 1);
         fence_barrier_init();
         fence_proxy_async();
     }
@@ -199,55 +340,186 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             umma_commit(tmem_full);  // accumulator complete
         }
     } else {
-        // epilogue: TMEM -> registers -> global (column-major, 128-byte coalesced per column)
-        const int quarter = warp & 3;
-        const int row = m0 + quarter * 32 + lane;
-        if (beta != 0.0f && m0 + quarter * 32 < M) {
-            // pull this warp's 32-row strip of the old C tile towards L2 while the main loop runs: for one column the
-            // strip is one 128-byte line; lane j takes columns j, j+32, ...
-            const float* strip = C + (size_t)(m0 + quarter * 32);
-            for (int c = lane; c < G_BN && n0 + c < N; c += 32)
-                asm volatile("prefetch.global.L2 [%0];\n" ::"l"(strip + (size_t)(n0 + c) * ldc));
-        }
-        if (KT > 0) {
-            mbar_wait(tmem_full, 0);
-            tc_fence_after();
-        }
-#pragma unroll 1
-        for (int c0 = 0; c0 < G_BN; c0 += 32) {
-            if (n0 + c0 >= N) break;  // warp-uniform
-            uint32_t v[32];
-            if (KT > 0) {
-                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = 0u;
-            }
-            if (row < M) {
-                float* base = C + (size_t)row + (size_t)(n0 + c0) * ldc;
-                const int ncols = min(32, N - (n0 + c0));
-                if (beta != 0.0f) {
-                    // all 32 loads of the chunk are issued before the first use: one DRAM round trip per chunk
-                    // instead of one per column
-                    float old[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) old[j] = (j < ncols) ? __ldcs(base + (size_t)j * ldc) : 0.0f;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]) + beta * old[j];
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < ncols) base[(size_t)j * ldc] = alpha * __uint_as_float(v[j]);
-                }
-            }
-        }
+        if (c_tma)
+            umma_epilogue_tma(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, &mapC, smem, cbar, tmem_full, C, ldc);
+        else
+            umma_epilogue(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, C, ldc, tmem_full);
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, G_TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CTA-pair variant: a cluster of two CTAs (the two SMs of a TPC) computes one 256 x 256 tile with
+// tcgen05.mma.cta_group::2 (M = 256, N = 256).  CTA r of the pair stages rows [128 r, 128 r + 128) of the A tile and
+// rows [128 r, 128 r + 128) of the (n-major) B tile; the tensor cores of both SMs read both halves of B, so each SM
+// pulls 32 KiB per 64 (bf16) k instead of 48 KiB from L2 and reads 8 KiB instead of 12 KiB of shared memory per UMMA.
+// Its accumulator half (its 128 rows x 256 columns) sits in its own TMEM.
+//   * both producers signal the LEADER's full barrier (TMA .cta_group::2 with the peer bit of the barrier address
+//     cleared); the leader's producer posts the expected bytes of both CTAs;
+//   * the leader's elected lane issues the MMAs and commits with .multicast::cluster to the empty / tmem_full barriers
+//     of both CTAs (same offsets in both);
+//   * TMEM is allocated and freed with .cta_group::2 by warp 1 of both CTAs, cluster barrier before the free.
+constexpr int P_STAGES_2CTA = 3, P_STAGES_1CTA = 6;
+#ifndef PB2_UMMA_DEFAULT_MODE
+#define PB2_UMMA_DEFAULT_MODE 3  // see launch_umma_gemm: 2 = two independent CTAs per SM, 3 = CTA pairs
+#endif
+constexpr int P_BH_BYTES = 128 * 128;  // this CTA's half of B: box [128 n][128 bytes of k]
+constexpr int P_STAGE_BYTES = G_A_BYTES + P_BH_BYTES;
+constexpr size_t pair_smem(int stages) { return (size_t)stages * P_STAGE_BYTES + 1024 + 512; }
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// TMA load issued by either CTA of the pair; completion bytes go to the barrier at `bar_cluster_addr` (a
+// shared::cluster address: the leader's barrier when the peer bit is cleared)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster_addr) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+template <int EB>
+__device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    if (EB == 2)
+        asm volatile(
+            "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+            "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d),
+            "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+            : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    const uint16_t mask = 3;
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(
+                     smem_u32(bar)),
+                 "h"(mask)
+                 : "memory");
+}
+
+template <int STAGES, int EB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G_THREADS, STAGES <= 3 ? 2 : 1)
+gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh, int M, int N, int K,
+               float alpha, float beta, float* __restrict__ C, int ldc, const __grid_constant__ CUtensorMap mapC, int c_tma) {
+    constexpr int BKE = 128 / EB;
+    constexpr int MBOX = 128 / EB;
+    constexpr int NBOX = G_BM / MBOX;
+    constexpr int BOX_BYTES = BKE * 128;
+    constexpr int UK = 32 / EB;
+    constexpr uint32_t IDESC = (1u << 4) | ((EB == 2 ? 1u : 2u) << 7) | ((EB == 2 ? 1u : 2u) << 10) | (1u << 15) |
+                               ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)((2 * G_BM) >> 4) << 24);
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase0 = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (sbase0 - raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * P_STAGE_BYTES);
+    uint64_t* empty = full + STAGES;
+    uint64_t* tmem_full = empty + STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    uint64_t* cbar = tmem_full + 2;  // 4 warps x E_NBUF barriers of the TMA-staged epilogue
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int pair = blockIdx.x >> 1;
+    const int pairs_m = (M + 2 * G_BM - 1) / (2 * G_BM);
+    const int m0 = (pair % pairs_m) * (2 * G_BM) + rank * G_BM;
+    const int n0 = (pair / pairs_m) * G_BN;
+    const int KT = (K + BKE - 1) / BKE;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);   // only the leader's is used: its producer's arrive + the bytes of both CTAs
+            mbar_init(&empty[s], 1);  // one multicast commit per refill
+        }
+        mbar_init(tmem_full, 1);
+        for (int i = 0; i < 4 * E_NBUF; ++i) mbar_init(&cbar[i], 1);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)G_TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::);
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();  // barriers of both CTAs initialised, TMEM of both allocated
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0 && KT > 0) {
+            tma_prefetch_desc(&mapA);
+            tma_prefetch_desc(&mapBh);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = 0; kt < KT; ++kt) {
+                if (kt >= STAGES) mbar_wait(&empty[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * P_STAGE_BYTES;
+                if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * P_STAGE_BYTES);
+                const uint32_t lead_full = smem_u32(&full[stage]) & 0xFEFFFFFFu;
+#pragma unroll
+                for (int b = 0; b < NBOX; ++b)
+                    tma_load_2d_pair(sa + b * BOX_BYTES, &mapA, m0 + b * MBOX, kt * BKE, lead_full);
+                tma_load_2d_pair(sa + G_A_BYTES, &mapBh, kt * BKE, n0 + rank * (G_BN / 2), lead_full);
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kt = 0; kt < KT; ++kt) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = sbase0 + stage * P_STAGE_BYTES;
+                const uint32_t sb = sa + G_A_BYTES;
+#pragma unroll
+                for (int ku = 0; ku < BKE / UK; ++ku) {
+                    const uint64_t adesc = EB == 2 ? umma_desc(sa + ku * UK * 128, BOX_BYTES, 1024, 2)
+                                                   : umma_desc(sa + ku * UK * 128, BOX_BYTES, 512, 1);
+                    const uint64_t bdesc = umma_desc(sb + ku * 32, 16, 1024);
+                    umma_pair<EB>(tmem_base, adesc, bdesc, IDESC, (kt | ku) != 0);
+                }
+                umma_commit_pair(&empty[stage]);
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            umma_commit_pair(tmem_full);
+        }
+    } else {
+        if (c_tma)
+            umma_epilogue_tma(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, &mapC, smem, cbar, tmem_full, C, ldc);
+        else
+            umma_epilogue(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, C, ldc, tmem_full);
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();  // the peer's MMAs read this CTA's shared memory and TMEM is freed as a pair
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"((uint32_t)G_TMEM_COLS));
     }
 }
 
@@ -275,8 +547,10 @@ static int umma_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, in
     const uint32_t row = 128 / eb;  // elements in one 128-byte swizzle row
     // the MN-major fp32 (TF32) operand needs the 32-byte-atom flavour of the 128-byte swizzle (see umma_desc)
     const CUtensorMapSwizzle swa = eb == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
-    int rc = kind == 0 ? encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, row, swa)
-                       : encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, G_BN, CU_TENSOR_MAP_SWIZZLE_128B);
+    int rc = kind == 3 ? encode_tmap_2d(&e.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, p, d0, d1, ld, 32, 32, CU_TENSOR_MAP_SWIZZLE_NONE)
+           : kind == 0 ? encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, row, swa)
+                       : encode_tmap_2d(&e.m, dt, eb, p, d0, d1, ld, row, kind == 2 ? G_BN / 2 : G_BN,
+                                        CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) {
         e.valid = false;
         return rc;
@@ -309,25 +583,57 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
             return PB2_ERR_CUDA;
         attr_set[dev] = true;
     }
-    // PB2_GEMM_BF16_CTAS=1 selects the deep single-CTA ring (kept for A/B runs); default: two CTAs per SM
+    // PB2_GEMM_BF16_CTAS: 1 = deep single-CTA ring, one CTA per SM; 2 = two independent CTAs per SM;
+    // pair = cta_group::2 CTA pairs, two pairs per TPC; pair1 = CTA pairs with the deep ring (kept for A/B runs)
     static int ctas = -1;
     if (ctas < 0) {
         const char* e = getenv("PB2_GEMM_BF16_CTAS");
-        ctas = (e && e[0] == '1') ? 1 : 2;
+        ctas = !e ? PB2_UMMA_DEFAULT_MODE : !strcmp(e, "1") ? 1 : !strcmp(e, "pair") ? 3 : !strcmp(e, "pair1") ? 4 : 2;
     }
     CUtensorMap ma, mb;
-    if (k > 0 && (umma_tmap(&ma, A, m, k, lda, 0, EB) || umma_tmap(&mb, B, k, n, ldb, 1, EB))) return PB2_ERR_CUDA;
+    if (k > 0 && (umma_tmap(&ma, A, m, k, lda, 0, EB) || umma_tmap(&mb, B, k, n, ldb, ctas >= 3 ? 2 : 1, EB)))
+        return PB2_ERR_CUDA;
     if (k == 0) {  // nothing to stage: the kernel only scales C; the maps are never dereferenced
         memset(&ma, 0, sizeof(ma));
         memset(&mb, 0, sizeof(mb));
     }
+    // C through TMA (boxes of 32 rows x 32 columns) when its base and pitch allow it; PB2_GEMM_EPILOGUE=direct keeps
+    // the register epilogue for A/B runs
+    static int epi_direct = -1;
+    if (epi_direct < 0) {
+        const char* e = getenv("PB2_GEMM_EPILOGUE");
+        epi_direct = (e && !strcmp(e, "direct")) ? 1 : 0;
+    }
+    CUtensorMap mc;
+    int c_tma = (!epi_direct && !(((uintptr_t)C) & 15) && !(ldc & 3)) ? 1 : 0;
+    if (c_tma && umma_tmap(&mc, C, m, n, ldc, 3, 4)) return PB2_ERR_CUDA;
+    if (!c_tma) memset(&mc, 0, sizeof(mc));
+    if (ctas >= 3) {
+        static bool pair_attr_set[64] = {false};
+        if (dev < 64 && !pair_attr_set[dev]) {
+            if (cudaFuncSetAttribute(gemm_umma_pair<P_STAGES_2CTA, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)pair_smem(P_STAGES_2CTA)) != cudaSuccess ||
+                cudaFuncSetAttribute(gemm_umma_pair<P_STAGES_1CTA, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)pair_smem(P_STAGES_1CTA)) != cudaSuccess)
+                return PB2_ERR_CUDA;
+            pair_attr_set[dev] = true;
+        }
+        dim3 pgrid(2 * ((m + 2 * G_BM - 1) / (2 * G_BM)) * ((n + G_BN - 1) / G_BN));
+        if (ctas == 3)
+            gemm_umma_pair<P_STAGES_2CTA, EB><<<pgrid, G_THREADS, pair_smem(P_STAGES_2CTA), (cudaStream_t)stream>>>(
+                ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
+        else
+            gemm_umma_pair<P_STAGES_1CTA, EB><<<pgrid, G_THREADS, pair_smem(P_STAGES_1CTA), (cudaStream_t)stream>>>(
+                ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
+        return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+    }
     dim3 grid(((m + G_BM - 1) / G_BM) * ((n + G_BN - 1) / G_BN));
     if (ctas == 1)
         gemm_bf16_tcgen05<G_STAGES_1CTA, EB><<<grid, G_THREADS, gemm_smem(G_STAGES_1CTA), (cudaStream_t)stream>>>(
-            ma, mb, m, n, k, alpha, beta, C, ldc);
+            ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
     else
         gemm_bf16_tcgen05<G_STAGES_2CTA, EB><<<grid, G_THREADS, gemm_smem(G_STAGES_2CTA), (cudaStream_t)stream>>>(
-            ma, mb, m, n, k, alpha, beta, C, ldc);
+            ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
     return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
 }
 

@@ -17,13 +17,13 @@ def _bf16_bits(x):
     return (u >> 16).astype(np.uint16)
 
 
-def _run(m, n, k, alpha, beta, seed=0, ld_pad=0):
+def _run(m, n, k, alpha, beta, seed=0, ld_pad=0, ldc_extra=0):
     import torch
     rng = np.random.default_rng(seed)
     A = np.asfortranarray(_bf16_bits(rng.uniform(-0.5, 0.5, (m, k))))
     B = np.asfortranarray(_bf16_bits(rng.uniform(-0.5, 0.5, (k, n))))
     Cm = np.asfortranarray(rng.uniform(-0.5, 0.5, (m, n)).astype(np.float32))
-    lda, ldb, ldc = m + ld_pad, k + ld_pad, m + ld_pad
+    lda, ldb, ldc = m + ld_pad, (k if k else 8) + ld_pad, m + ld_pad + ldc_extra
 
     def to_dev(X, ld, dtype):
         buf = np.zeros((X.shape[1], ld), dtype=dtype)
@@ -39,7 +39,7 @@ def _run(m, n, k, alpha, beta, seed=0, ld_pad=0):
     want = Cm.copy(order="F")
     O.lib().orc_gemm_tile_bf16(m, n, k, alpha, A.ctypes.data, m, B.ctypes.data, k, beta, want.ctypes.data, m)
     back = lambda X: (X.astype(np.uint32) << 16).view(np.float32).astype(np.float64)
-    inf = lambda X: np.abs(X).sum(axis=1).max()
+    inf = lambda X: np.abs(X).sum(axis=1).max() if X.size else 0.0
     denom = max(abs(alpha) * inf(back(A)) * inf(back(B)) * max(k, 1) * EPS32, 1e-30)
     return inf(got.astype(np.float64) - want.astype(np.float64)) / denom
 
@@ -62,6 +62,23 @@ def test_alpha_beta(alpha, beta):
 
 def test_padded_leading_dimension():
     assert _run(256, 256, 128, 1.0, 1.0, seed=4, ld_pad=8) < 10
+
+
+@pytest.mark.parametrize("m,n,k,beta", [(256, 256, 128, 1.0), (200, 136, 72, 0.5), (136, 300, 16, 0.0)])
+def test_c_pitch_not_a_multiple_of_16_bytes_takes_the_register_epilogue(m, n, k, beta):
+    # C goes through TMA boxes only when its base is 16-byte aligned and ldc % 4 == 0; any other C is still accepted
+    assert _run(m, n, k, 1.0, beta, seed=m, ldc_extra=1) < 10
+
+
+@pytest.mark.parametrize("beta", [0.0, 1.0, -0.25])
+def test_k_zero_scales_c(beta):
+    assert _run(200, 300, 0, 1.0, beta, seed=5) < 10
+
+
+@pytest.mark.parametrize("m,n,k,beta", [(2048, 2048, 512, 1.0), (1000, 520, 264, 0.0), (40, 1000, 64, 2.0)])
+def test_more_column_chunks_than_staging_buffers(m, n, k, beta):
+    # 256 columns per CTA = 8 boxes of 32 against 6 buffers per warp: the last two recycle a buffer
+    assert _run(m, n, k, 0.5, beta, seed=k) < 10
 
 
 def test_unsupported_arguments():
