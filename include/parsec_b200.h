@@ -70,7 +70,9 @@ int parsec_b200_dgemm(char transa, char transb, int m, int n, int k, double alph
 
 /* BF16-in / FP32-accumulate tile GEMM on tcgen05 + TMEM fed by TMA (BASELINE config 5).  Same argument meaning as
  * cublasGemmEx(CUDA_R_16BF, CUDA_R_16BF, CUDA_R_32F, CUBLAS_COMPUTE_32F): A, B are bf16, C is fp32, column-major.
- * The reference has no bf16 body; the call shape follows its cublasDgemm_v2 bodies. */
+ * The reference has no bf16 body; the call shape follows its cublasDgemm_v2 bodies.  transa = transb = 'N' only
+ * (PB2_ERR_NOT_SUPPORTED otherwise); A and B 16-byte aligned with lda, ldb multiples of 8.  C may be any fp32
+ * matrix; when its base is 16-byte aligned and ldc is a multiple of 4 it is moved by TMA, which is the fast path. */
 int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A, int lda,
                                 const void* B, int ldb, float beta, float* C, int ldc, void* stream);
 
