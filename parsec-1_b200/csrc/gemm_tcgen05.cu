@@ -113,6 +113,27 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
+// -DPB2_UMMA_TRACE (tools/umma_trace.cu only): per-CTA globaltimer marks of gemm_umma_pair -- 0 entry, 1 set-up done
+// (barriers, TMEM, cluster sync), 2 accumulator complete, 3 epilogue done -- plus the SM id; the slot index lives in the
+// word after the epilogue barriers.  Compiled out of the library.
+#ifdef PB2_UMMA_TRACE
+__device__ unsigned long long pb2_trace_buf[5 * 65536];
+__device__ unsigned int pb2_trace_n;
+__device__ __forceinline__ unsigned long long pb2_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+    return t;
+}
+#define PB2_TRACE_MARK(cbar_, which_, cond_)                                                       \
+    do {                                                                                           \
+        if (cond_) pb2_trace_buf[5 * ((cbar_)[4 * E_NBUF] & 65535) + (which_)] = pb2_now();        \
+    } while (0)
+#else
+#define PB2_TRACE_MARK(cbar_, which_, cond_) \
+    do {                                     \
+    } while (0)
+#endif
+
 // epilogue of one warp: TMEM -> registers -> global (column-major, 128-byte coalesced per column); `quarter` selects
 // the 32 TMEM lanes (rows of the tile) this warp may touch
 __device__ __forceinline__ void umma_epilogue(uint32_t tmem_base, int quarter, int lane, int m0, int n0, int M, int N, int KT,
@@ -198,6 +219,7 @@ __device__ __forceinline__ void umma_epilogue_tma(uint32_t tmem_base, int quarte
         mbar_wait(tmem_full, 0);  // every MMA has completed: the operand ring is no longer read
         tc_fence_after();
     }
+    PB2_TRACE_MARK(cbar, 2, quarter == 0 && lane == 0);
     if (!live) return;
     float* bufs = reinterpret_cast<float*>(ring + quarter * (E_NBUF * E_BOX_BYTES));
     uint64_t* bar = cbar + quarter * E_NBUF;
@@ -441,6 +463,16 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int m0 = (pair % pairs_m) * (2 * G_BM) + rank * G_BM;
     const int n0 = (pair / pairs_m) * G_BN;
     const int KT = (K + BKE - 1) / BKE;
+#ifdef PB2_UMMA_TRACE
+    if (threadIdx.x == 128) {
+        const unsigned slot = atomicAdd(&pb2_trace_n, 1u);
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;\n" : "=r"(smid));
+        cbar[4 * E_NBUF] = slot;
+        pb2_trace_buf[5 * (slot & 65535) + 0] = pb2_now();
+        pb2_trace_buf[5 * (slot & 65535) + 4] = ((unsigned long long)blockIdx.x << 32) | smid;
+    }
+#endif
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -461,6 +493,7 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     tc_fence_before();
     cluster_sync_all();  // barriers of both CTAs initialised, TMEM of both allocated
     tc_fence_after();
+    PB2_TRACE_MARK(cbar, 1, threadIdx.x == 128);
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
@@ -513,6 +546,7 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             umma_epilogue_tma(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, &mapC, smem, cbar, tmem_full, C, ldc);
         else
             umma_epilogue(tmem_base, warp & 3, lane, m0, n0, M, N, KT, alpha, beta, C, ldc, tmem_full);
+        PB2_TRACE_MARK(cbar, 3, warp == 4 && lane == 0);
     }
     __syncwarp();
     tc_fence_before();
