@@ -485,15 +485,24 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         fence_proxy_async();
     }
     if (warp == 1) {
+#ifdef PB2_UMMA_TRACE
+        const unsigned long long ta = pb2_now();
+#endif
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)),
                      "r"((uint32_t)G_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::);
+#ifdef PB2_UMMA_TRACE
+        if (lane == 0) cbar[4 * E_NBUF + 1] = pb2_now() - ta;  // how long the TMEM allocation took
+#endif
     }
     __syncwarp();
     tc_fence_before();
     cluster_sync_all();  // barriers of both CTAs initialised, TMEM of both allocated
     tc_fence_after();
     PB2_TRACE_MARK(cbar, 1, threadIdx.x == 128);
+#ifdef PB2_UMMA_TRACE
+    if (threadIdx.x == 128) pb2_trace_buf[5 * (cbar[4 * E_NBUF] & 65535) + 4] |= (cbar[4 * E_NBUF + 1] & 0xFFFFF) << 44;
+#endif
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {

@@ -75,6 +75,9 @@ int main(int argc, char** argv) {
         printf("  %-48s mean %7.2f us  p10 %7.2f  p50 %7.2f  p90 %7.2f\n", names[k], p[k] / n, d[k][n / 10], d[k][n / 2],
                d[k][n * 9 / 10]);
     }
+    double alloc = 0;
+    for (unsigned i = 0; i < n; ++i) alloc += (double)(buf[5 * i + 4] >> 44) * 1e-3;
+    printf("  of the set-up, tcgen05.alloc took            mean %7.2f us\n", alloc / n);
     printf("  CTA lifetime mean %.2f us; ideal main loop alone: %.2f us at 8192 flop/clk/SM, 1.92 GHz\n", (p[0] + p[1] + p[2]) / n,
            2.0 * 128 * 256 * nb / 8192 / 1920.0);
     // one SM's timeline
@@ -83,7 +86,7 @@ int main(int argc, char** argv) {
     for (unsigned i = 0; i < n; ++i)
         if ((unsigned)(buf[5 * i + 4] & 0xffffffffu) == sm)
             rows.push_back({(buf[5 * i] - tmin) * 1e-3, (buf[5 * i + 1] - tmin) * 1e-3, (buf[5 * i + 2] - tmin) * 1e-3,
-                            (buf[5 * i + 3] - tmin) * 1e-3, (double)(buf[5 * i + 4] >> 32)});
+                            (buf[5 * i + 3] - tmin) * 1e-3, (double)((buf[5 * i + 4] >> 32) & 0xFFF)});
     std::sort(rows.begin(), rows.end());
     printf("  SM %u ran %zu CTAs; entry / set-up done / accumulator complete / done (us), block:\n", sm, rows.size());
     for (size_t i = 0; i < rows.size() && i < 24; ++i)
