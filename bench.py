@@ -161,6 +161,11 @@ def main():
         run_reference(args, rank)
         return
 
+    # stdout carries exactly one JSON line.  Libraries write there too (NCCL prints its version banner with
+    # NCCL_DEBUG=VERSION), so file descriptor 1 points at stderr until the line is printed.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
@@ -323,7 +328,10 @@ def main():
         m.close()
     dev.close()
     if rank == 0:
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(out), flush=True)
+        os.dup2(2, 1)
     if comm is not None:
         comm.close()
     if world > 1:
