@@ -289,7 +289,9 @@ typedef struct pb2_gemm_stats_s {
 
 pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, pb2_matrix_block_cyclic_t* B,
                                       pb2_matrix_block_cyclic_t* C, pb2_device_t* dev);
-/* knobs (before run): chains in flight, exec-side dtype path */
+/* knobs (before run): "window" = C-tile chains in flight (0 = all, -1 = default: 128, or 16 for tensor-core
+ * bodies); "bcast_lookahead" = k-steps the broadcast plan is issued ahead of the GEMMs (default 4, 0 = whole plan at
+ * start).  PB2_ERR_NOT_FOUND for an unknown key. */
 int pb2_gemm_taskpool_set(pb2_taskpool_t* tp, const char* key, int64_t value);
 /* ------------------------------------------------------------------------------------------------
  * Intra-box tile data plane (piece 3): NCCL broadcasts along the rows / columns of the P x Q grid.  Replaces, for
