@@ -393,6 +393,8 @@ constexpr int P_STAGES_2CTA = 3, P_STAGES_1CTA = 6;
 constexpr int P_BH_BYTES = 128 * 128;  // this CTA's half of B: box [128 n][128 bytes of k]
 constexpr int P_STAGE_BYTES = G_A_BYTES + P_BH_BYTES;
 constexpr size_t pair_smem(int stages) { return (size_t)stages * P_STAGE_BYTES + 1024 + 512; }
+static_assert(P_STAGES_2CTA * P_STAGE_BYTES >= E_RING_BYTES && G_STAGES_2CTA * G_STAGE_BYTES >= E_RING_BYTES,
+              "the TMA-staged epilogue borrows 96 KiB of the operand ring");
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
