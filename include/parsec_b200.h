@@ -253,7 +253,8 @@ int pb2_matrix_set_mat(pb2_matrix_block_cyclic_t* dc, void* mat);
 int64_t pb2_matrix_nb_local_tiles(const pb2_matrix_block_cyclic_t* dc);
 int pb2_matrix_mt(const pb2_matrix_block_cyclic_t* dc);
 int pb2_matrix_nt(const pb2_matrix_block_cyclic_t* dc);
-/* twoDBC_rank_of (:258-286), local tile position (:333-349), data_of (:368-412), data_key (matrix.c) */
+/* twoDBC_rank_of (:258-286), local tile position (:333-349), data_of (:368-412), data_key (matrix.c); with kp or
+ * kq > 1 their k-cyclic counterparts twoDBC_kcyclic_rank_of (:532-566) and twoDBC_kcyclic_data_of (:634-680) */
 int pb2_matrix_rank_of(const pb2_matrix_block_cyclic_t* dc, int m, int n);
 int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int m, int n);
 uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n);

@@ -94,20 +94,39 @@ void orc_bc_init(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i
 int orc_bc_rank_of(const orc_bc_t* dc, int m, int n) {
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
-    int rr = (m % dc->P + dc->ip) % dc->P;
-    int cr = (n % dc->Q + dc->jq) % dc->Q;
+    /* (m, n) lies in k-cyclic super-tile (m / kp, n / kq): two_dim_rectangle_cyclic.c:532-566; with kp = kq = 1 this
+     * is twoDBC_rank_of, :258-286 */
+    int rr = ((m / dc->kp) % dc->P + dc->ip) % dc->P;
+    int cr = ((n / dc->kq) % dc->Q + dc->jq) % dc->Q;
     return rr * dc->Q + cr;
 }
 
 int orc_bc_position(const orc_bc_t* dc, int m, int n) {
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
-    return dc->nb_elem_r * (n / dc->Q) + (m / dc->P);
+    /* twoDBC_kcyclic_data_of, :652-664 (twoDBC_coordinates_to_position, :333-349, when kp = kq = 1) */
+    int local_m = (m / (dc->kp * dc->P)) * dc->kp + (m % (dc->kp * dc->P)) % dc->kp;
+    int local_n = (n / (dc->kq * dc->Q)) * dc->kq + (n % (dc->kq * dc->Q)) % dc->kq;
+    return dc->nb_elem_r * local_n + local_m;
 }
 
 uint64_t orc_bc_key(const orc_bc_t* dc, int m, int n) {
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
+    return (uint64_t)n * (uint64_t)dc->lmt + (uint64_t)m;
+}
+
+/* The key stored in the parsec_data_t that data_of creates.  Plain cyclic: the data key.  k-cyclic:
+ * twoDBC_kcyclic_data_of reduces m and n modulo the super-tile period while it computes the local position
+ * (:652-664) and then builds the key from the REDUCED coordinates (:676-678), so tiles one period apart share a
+ * key.  Reproduced as it is (the reference's own behaviour is the contract), see DESIGN.md. */
+uint64_t orc_bc_data_of_key(const orc_bc_t* dc, int m, int n) {
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    if (dc->kp > 1 || dc->kq > 1) {
+        m %= dc->kp * dc->P;
+        n %= dc->kq * dc->Q;
+    }
     return (uint64_t)n * (uint64_t)dc->lmt + (uint64_t)m;
 }
 

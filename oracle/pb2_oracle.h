@@ -49,6 +49,7 @@ void orc_bc_init(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i
 int orc_bc_rank_of(const orc_bc_t* dc, int m, int n);
 int orc_bc_position(const orc_bc_t* dc, int m, int n);
 uint64_t orc_bc_key(const orc_bc_t* dc, int m, int n);
+uint64_t orc_bc_data_of_key(const orc_bc_t* dc, int m, int n); /* key of the parsec_data_t data_of creates */
 void orc_bc_key2coords(const orc_bc_t* dc, uint64_t key, int* m, int* n);
 /* fill every locally stored tile of a PARSEC_MATRIX_TILE-storage matrix (mat holds nb_local_tiles*bsiz doubles) */
 void orc_bc_fill(const orc_bc_t* dc, double* mat, unsigned seed, int nthreads);

@@ -36,9 +36,6 @@ extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int
     if (mb <= 0 || nb <= 0 || lm <= 0 || ln <= 0 || m <= 0 || n <= 0 || P <= 0 || Q <= 0 || kp <= 0 || kq <= 0 ||
         myrank < 0 || myrank >= P * Q || i < 0 || j < 0 || i + m > lm || j + n > ln)
         return nullptr;
-    // k-cyclic distributions go through the reference's kview remapping (:440-520); the tiled GEMM path and
-    // every BASELINE config use kp = kq = 1, so anything else is refused rather than half-supported.
-    if (kp != 1 || kq != 1) return nullptr;
     int es = mtype == PB2_MATRIX_DOUBLE ? 8 : mtype == PB2_MATRIX_FLOAT ? 4 : mtype == PB2_MATRIX_BF16 ? 2 : 0;
     if (!es) return nullptr;
     auto* dc = new pb2_matrix_block_cyclic_s();
@@ -88,14 +85,19 @@ extern "C" int pb2_matrix_rank_of(const pb2_matrix_block_cyclic_t* dc, int m, in
     if (!dc || m < 0 || n < 0 || m >= dc->mt || n >= dc->nt) return PB2_ERR_BAD_PARAM;
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
-    return ((m % dc->P + dc->ip) % dc->P) * dc->Q + (n % dc->Q + dc->jq) % dc->Q;
+    // (m, n) lies in k-cyclic super-tile (m / kp, n / kq): twoDBC_kcyclic_rank_of (:532-566), which is twoDBC_rank_of
+    // (:258-286) when kp = kq = 1
+    return (((m / dc->kp) % dc->P + dc->ip) % dc->P) * dc->Q + ((n / dc->kq) % dc->Q + dc->jq) % dc->Q;
 }
 
 extern "C" int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
     if (!dc || m < 0 || n < 0 || m >= dc->mt || n >= dc->nt) return PB2_ERR_BAD_PARAM;
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
-    return (int64_t)dc->nb_elem_r * (n / dc->Q) + (m / dc->P);
+    // twoDBC_kcyclic_data_of (:652-664); twoDBC_coordinates_to_position (:333-349) when kp = kq = 1
+    const int local_m = (m / (dc->kp * dc->P)) * dc->kp + (m % (dc->kp * dc->P)) % dc->kp;
+    const int local_n = (n / (dc->kq * dc->Q)) * dc->kq + (n % (dc->kq * dc->Q)) % dc->kq;
+    return (int64_t)dc->nb_elem_r * local_n + local_m;
 }
 
 extern "C" uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
@@ -110,8 +112,14 @@ extern "C" pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, 
     std::lock_guard<std::mutex> g(dc->lock);
     if (!dc->data_map[(size_t)pos]) {
         char* ptr = dc->mat ? (char*)dc->mat + (size_t)pos * dc->bsiz * dc->elem_size : nullptr;
-        dc->data_map[(size_t)pos] =
-            pb2_data_create(pb2_matrix_data_key(dc, m, n), dc->dc_id, ptr, (uint32_t)((size_t)dc->bsiz * dc->elem_size));
+        // key of the parsec_data_t: the data key, except that twoDBC_kcyclic_data_of builds it from the coordinates it
+        // has just reduced modulo the super-tile period (:652-678); kept as the reference has it
+        uint64_t key = pb2_matrix_data_key(dc, m, n);
+        if (dc->kp > 1 || dc->kq > 1) {
+            const int gm = (m + dc->i / dc->mb) % (dc->kp * dc->P), gn = (n + dc->j / dc->nb) % (dc->kq * dc->Q);
+            key = (uint64_t)gn * (uint64_t)dc->lmt + (uint64_t)gm;
+        }
+        dc->data_map[(size_t)pos] = pb2_data_create(key, dc->dc_id, ptr, (uint32_t)((size_t)dc->bsiz * dc->elem_size));
     }
     return dc->data_map[(size_t)pos];
 }
@@ -126,10 +134,11 @@ extern "C" int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_d
 }
 
 // accessors for the taskpool (same translation unit family; not part of the public header)
-extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out /*[12]*/) {
+extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out /*[14]*/) {
     if (!dc || !out) return PB2_ERR_BAD_PARAM;
-    int v[12] = {dc->mtype, dc->elem_size, dc->mb, dc->nb, dc->m, dc->n, dc->mt, dc->nt, dc->P, dc->Q, dc->myrank, (int)dc->dc_id};
-    for (int i = 0; i < 12; ++i) out[i] = v[i];
+    int v[14] = {dc->mtype, dc->elem_size, dc->mb, dc->nb, dc->m, dc->n, dc->mt, dc->nt, dc->P, dc->Q, dc->myrank, (int)dc->dc_id,
+                 dc->kp, dc->kq};
+    for (int i = 0; i < 14; ++i) out[i] = v[i];
     return PB2_SUCCESS;
 }
 

@@ -36,12 +36,12 @@ int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data);
 }
 
 struct Geo {
-    int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id;
+    int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id, kp, kq;
 };
 static Geo geo_of(const pb2_matrix_block_cyclic_t* dc) {
-    int v[12];
+    int v[14];
     pb2_matrix_geometry(dc, v);
-    return Geo{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11]};
+    return Geo{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11], v[12], v[13]};
 }
 
 struct pb2_taskpool_s {
@@ -182,7 +182,11 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
     bool types = (tp->gC.mtype == PB2_MATRIX_DOUBLE && tp->gA.mtype == PB2_MATRIX_DOUBLE) ||
                  (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16) ||
                  (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_FLOAT);  // fp32 tiles: TF32 tensor cores
-    if (!ok || !types) {
+    // the row / column broadcast plan is written for plain cyclic ownership (tile row m on process row m mod P); the
+    // descriptors themselves map k-cyclic layouts exactly as the reference does, and one rank runs them unchanged
+    bool cyclic = tp->gC.P * tp->gC.Q == 1 || (tp->gA.kp == 1 && tp->gA.kq == 1 && tp->gB.kp == 1 && tp->gB.kq == 1 &&
+                                                tp->gC.kp == 1 && tp->gC.kq == 1);
+    if (!ok || !types || !cyclic) {
         delete tp;
         return nullptr;
     }

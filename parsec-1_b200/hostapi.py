@@ -169,8 +169,8 @@ class Device:
 class Matrix:
     """parsec_matrix_block_cyclic_t in tile storage, backed by a host buffer (numpy array or raw pointer)."""
 
-    def __init__(self, mtype, M, N, mb, nb, P=1, Q=1, rank=0, buf=None):
-        self.h = C.c_void_p(lib().pb2_matrix_block_cyclic_new(mtype, rank, mb, nb, M, N, 0, 0, M, N, P, Q, 1, 1, 0, 0))
+    def __init__(self, mtype, M, N, mb, nb, P=1, Q=1, rank=0, buf=None, kp=1, kq=1, ip=0, jq=0):
+        self.h = C.c_void_p(lib().pb2_matrix_block_cyclic_new(mtype, rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq))
         if not self.h:
             raise ValueError("pb2_matrix_block_cyclic_new rejected the arguments")
         self.mtype, self.M, self.N, self.mb, self.nb = mtype, M, N, mb, nb

@@ -176,10 +176,17 @@ def block_cyclic_cases():
     ref.ref_bc_tile_offset.restype = C.c_int64
     ref.ref_bc_tile_offset.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
     cases = []
-    for (M, N, mb, nb) in [(2048, 2048, 256, 256), (1000, 1000, 96, 96), (250, 130, 40, 40), (640, 384, 64, 128)]:
-        for (P, Q) in [(1, 1), (1, 2), (2, 2), (2, 4), (3, 2)]:
+    plain = [(M, N, mb, nb, P, Q, 1, 1, 0, 0)
+             for (M, N, mb, nb) in [(2048, 2048, 256, 256), (1000, 1000, 96, 96), (250, 130, 40, 40), (640, 384, 64, 128)]
+             for (P, Q) in [(1, 1), (1, 2), (2, 2), (2, 4), (3, 2)]]
+    # k-cyclic super-tiles (twoDBC_kcyclic_*) and a shifted process-grid origin (ip, jq)
+    kcyc = [(M, N, mb, nb, P, Q, kp, kq, ip, jq)
+            for (M, N, mb, nb) in [(1000, 1000, 96, 96), (640, 384, 64, 128)]
+            for (P, Q, kp, kq, ip, jq) in [(1, 1, 2, 3, 0, 0), (2, 2, 2, 1, 0, 0), (2, 3, 2, 3, 0, 0), (3, 2, 3, 2, 1, 1),
+                                           (2, 2, 1, 1, 1, 0)]]
+    for (M, N, mb, nb, P, Q, kp, kq, ip, jq) in plain + kcyc:
             for rank in range(P * Q):
-                dc = ref.ref_bc_new(rank, mb, nb, M, N, 0, 0, M, N, P, Q, 1, 1, 0, 0)
+                dc = ref.ref_bc_new(rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq)
                 g = (C.c_int * 14)()
                 ref.ref_bc_geometry(dc, g)
                 geo = dict(zip("mt nt lmt lnt lm ln llm lln bsiz nb_elem_r nb_elem_c nb_local_tiles rrank crank".split(), list(g)))
@@ -193,7 +200,8 @@ def block_cyclic_cases():
                             off = ref.ref_bc_tile_offset(dc, m, n, C.byref(key), C.byref(nbe))
                             entry += [int(off), int(key.value), int(nbe.value)]
                         tiles.append(entry)
-                cases.append({"M": M, "N": N, "mb": mb, "nb": nb, "P": P, "Q": Q, "rank": rank, "geo": geo, "tiles": tiles})
+                cases.append({"M": M, "N": N, "mb": mb, "nb": nb, "P": P, "Q": Q, "kp": kp, "kq": kq, "ip": ip, "jq": jq,
+                              "rank": rank, "geo": geo, "tiles": tiles})
     json.dump(cases, open(os.path.join(HERE, "block_cyclic.json"), "w"))
     print("wrote block_cyclic.json (%d descriptors, %d tiles)" % (len(cases), sum(len(c["tiles"]) for c in cases)))
 

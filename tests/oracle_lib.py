@@ -45,6 +45,8 @@ def lib():
         L.orc_bc_position.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
         L.orc_bc_key.restype = C.c_uint64
         L.orc_bc_key.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
+        L.orc_bc_data_of_key.restype = C.c_uint64
+        L.orc_bc_data_of_key.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
         L.orc_bc_fill.argtypes = [C.POINTER(BC), C.c_void_p, C.c_uint, C.c_int]
         L.orc_dgemm_tile.argtypes = [C.c_int] * 3 + [C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                                      C.c_double, C.c_void_p, C.c_int]

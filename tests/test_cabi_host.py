@@ -70,8 +70,22 @@ def test_descriptor_argument_errors():
     L = H.lib()
     assert not L.pb2_matrix_block_cyclic_new(0, 0, 0, 4, 8, 8, 0, 0, 8, 8, 1, 1, 1, 1, 0, 0)   # mb = 0
     assert not L.pb2_matrix_block_cyclic_new(0, 4, 4, 4, 8, 8, 0, 0, 8, 8, 2, 2, 1, 1, 0, 0)   # rank >= P*Q
-    assert not L.pb2_matrix_block_cyclic_new(0, 0, 4, 4, 8, 8, 0, 0, 8, 8, 1, 1, 2, 1, 0, 0)   # k-cyclic refused
+    assert not L.pb2_matrix_block_cyclic_new(0, 0, 4, 4, 8, 8, 0, 0, 8, 8, 1, 1, 0, 1, 0, 0)   # kp = 0
     assert not L.pb2_matrix_block_cyclic_new(9, 0, 4, 4, 8, 8, 0, 0, 8, 8, 1, 1, 1, 1, 0, 0)   # unknown mtype
+
+
+def test_k_cyclic_descriptors_map_but_only_plain_cyclic_grids_run_distributed():
+    """kp, kq > 1 are mapped exactly as the reference maps them (tests/test_block_cyclic_golden.py); the P x Q taskpool's
+    broadcast plan is written for plain cyclic ownership, so it takes k-cyclic descriptors on one rank only."""
+    L = H.lib()
+    one = [H.Matrix(H.MATRIX_DOUBLE, 64, 64, 8, 8, 1, 1, 0, kp=2, kq=3) for _ in range(3)]
+    tp = L.pb2_gemm_taskpool_new(one[0].h, one[1].h, one[2].h, C.c_void_p(1))   # dev is only stored by _new
+    assert tp
+    L.pb2_gemm_taskpool_free(C.c_void_p(tp))
+    grid = [H.Matrix(H.MATRIX_DOUBLE, 64, 64, 8, 8, 2, 2, 1, kp=2, kq=1) for _ in range(3)]
+    assert not L.pb2_gemm_taskpool_new(grid[0].h, grid[1].h, grid[2].h, C.c_void_p(1))
+    for m in one + grid:
+        m.close()
 
 
 def test_data_master_starts_like_parsec_data_create():
