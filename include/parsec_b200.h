@@ -316,6 +316,12 @@ typedef struct pb2_bcast_op_s {
     int32_t which, k, idx, root, i_am_root;
 } pb2_bcast_op_t;
 int64_t pb2_comm_plan(int P, int Q, int rank, int MT, int NT, int KT, pb2_bcast_op_t* out, int64_t max_ops);
+/* The same for k-cyclic descriptors and a shifted grid origin (twoDBC_kcyclic_rank_of,
+ * two_dim_rectangle_cyclic.c:532-566): tile rows of A and C dealt in super-tiles of kp, tile columns of B and C in
+ * super-tiles of kq, the k dimension in super-tiles of a_kq (columns of A) and b_kp (rows of B), origin (ip, jq).
+ * pb2_comm_plan is the case (1, 1, 1, 1, 0, 0). */
+int64_t pb2_comm_plan_ex(int P, int Q, int rank, int MT, int NT, int KT, int kp, int kq, int a_kq, int b_kp, int ip,
+                         int jq, pb2_bcast_op_t* out, int64_t max_ops);
 /* give a P x Q taskpool its communicator (must match the descriptors' grid and rank) */
 int pb2_gemm_taskpool_set_comm(pb2_taskpool_t* tp, pb2_comm_t* comm);
 

@@ -134,11 +134,11 @@ extern "C" int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_d
 }
 
 // accessors for the taskpool (same translation unit family; not part of the public header)
-extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out /*[14]*/) {
+extern "C" int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out /*[18]*/) {
     if (!dc || !out) return PB2_ERR_BAD_PARAM;
-    int v[14] = {dc->mtype, dc->elem_size, dc->mb, dc->nb, dc->m, dc->n, dc->mt, dc->nt, dc->P, dc->Q, dc->myrank, (int)dc->dc_id,
-                 dc->kp, dc->kq};
-    for (int i = 0; i < 14; ++i) out[i] = v[i];
+    int v[18] = {dc->mtype, dc->elem_size, dc->mb, dc->nb, dc->m, dc->n, dc->mt, dc->nt, dc->P, dc->Q, dc->myrank, (int)dc->dc_id,
+                 dc->kp, dc->kq, dc->ip, dc->jq, dc->i, dc->j};
+    for (int i = 0; i < 18; ++i) out[i] = v[i];
     return PB2_SUCCESS;
 }
 

@@ -154,21 +154,37 @@ extern "C" int pb2_comm_bcast(pb2_comm_t* c, int which, void* buf, size_t bytes,
 // Pure integer logic, no CUDA: tests/test_dist_gloo.py checks it across ranks on the CPU.
 // pb2_bcast_op_t: which (0 = row communicator / an A tile, 1 = column communicator / a B tile), k (GEMM step),
 // idx (m for A(m,k), n for B(k,n)), root (rank inside the communicator), i_am_root.
-extern "C" int64_t pb2_comm_plan(int P, int Q, int rank, int MT, int NT, int KT, pb2_bcast_op_t* out, int64_t max_ops) {
-    if (P <= 0 || Q <= 0 || rank < 0 || rank >= P * Q || MT <= 0 || NT <= 0 || KT <= 0) return PB2_ERR_BAD_PARAM;
+// General form: C (and the rows of A) dealt in super-tiles of kp tile rows, C (and the columns of B) in super-tiles of
+// kq tile columns, the k dimension in super-tiles of a_kq (columns of A) and b_kp (rows of B), process-grid origin
+// (ip, jq): twoDBC_kcyclic_rank_of, two_dim_rectangle_cyclic.c:532-566.  A(m,k) travels along the process row that owns
+// tile row m, from the process column that owns tile column k of A; B(k,n) along the process column that owns tile
+// column n, from the process row that owns tile row k of B.
+extern "C" int64_t pb2_comm_plan_ex(int P, int Q, int rank, int MT, int NT, int KT, int kp, int kq, int a_kq, int b_kp, int ip,
+                                    int jq, pb2_bcast_op_t* out, int64_t max_ops) {
+    if (P <= 0 || Q <= 0 || rank < 0 || rank >= P * Q || MT <= 0 || NT <= 0 || KT <= 0 || kp <= 0 || kq <= 0 || a_kq <= 0 ||
+        b_kp <= 0 || ip < 0 || ip >= P || jq < 0 || jq >= Q)
+        return PB2_ERR_BAD_PARAM;
     const int myrow = rank / Q, mycol = rank % Q;
     int64_t n = 0;
     for (int k = 0; k < KT; ++k) {
+        const int a_col = ((k / a_kq) % Q + jq) % Q, b_row = ((k / b_kp) % P + ip) % P;
         if (Q > 1)
-            for (int m = myrow; m < MT; m += P) {  // A(m,k): owner is (m mod P, k mod Q)
-                if (out && n < max_ops) out[n] = pb2_bcast_op_t{0, k, m, k % Q, (k % Q) == mycol};
+            for (int m = 0; m < MT; ++m) {
+                if (((m / kp) % P + ip) % P != myrow) continue;
+                if (out && n < max_ops) out[n] = pb2_bcast_op_t{0, k, m, a_col, a_col == mycol};
                 ++n;
             }
         if (P > 1)
-            for (int c = mycol; c < NT; c += Q) {  // B(k,c): owner is (k mod P, c mod Q)
-                if (out && n < max_ops) out[n] = pb2_bcast_op_t{1, k, c, k % P, (k % P) == myrow};
+            for (int c = 0; c < NT; ++c) {
+                if (((c / kq) % Q + jq) % Q != mycol) continue;
+                if (out && n < max_ops) out[n] = pb2_bcast_op_t{1, k, c, b_row, b_row == myrow};
                 ++n;
             }
     }
     return n;
+}
+
+// plain cyclic ownership: A(m,k) on (m mod P, k mod Q), B(k,n) on (k mod P, n mod Q)
+extern "C" int64_t pb2_comm_plan(int P, int Q, int rank, int MT, int NT, int KT, pb2_bcast_op_t* out, int64_t max_ops) {
+    return pb2_comm_plan_ex(P, Q, rank, MT, NT, KT, 1, 1, 1, 1, 0, 0, out, max_ops);
 }

@@ -36,12 +36,12 @@ int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data);
 }
 
 struct Geo {
-    int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id, kp, kq;
+    int mtype, es, mb, nb, m, n, mt, nt, P, Q, rank, dc_id, kp, kq, ip, jq, i, j;
 };
 static Geo geo_of(const pb2_matrix_block_cyclic_t* dc) {
-    int v[14];
+    int v[18];
     pb2_matrix_geometry(dc, v);
-    return Geo{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11], v[12], v[13]};
+    return Geo{v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11], v[12], v[13], v[14], v[15], v[16], v[17]};
 }
 
 struct pb2_taskpool_s {
@@ -62,7 +62,10 @@ struct pb2_taskpool_s {
     int64_t nb_gemm = 0, nb_read_a = 0, nb_read_b = 0;
     int status = 0;
     // tiles of A / B this rank's GEMMs read: local rows x KT and KT x local columns; remote ones are proxies
+    // row_slot[m] / col_slot[n]: index of tile row m / tile column n among the ones this rank's process row / column
+    // owns (-1: not mine), whatever the k-cyclicity and the grid origin
     std::vector<pb2_data_s*> a_tiles, b_tiles;
+    std::vector<int> row_slot, col_slot;
     std::vector<pb2_data_s*> proxies, pinned;
     std::vector<cudaEvent_t> comm_events;
     // the broadcast plan (canonical order, k ascending) and how far it has been issued.  Group k is issued no later than
@@ -75,8 +78,8 @@ struct pb2_taskpool_s {
     int64_t bcast_lookahead = 4;
 };
 
-static pb2_data_s* a_tile(pb2_taskpool_s* tp, int m, int k) { return tp->a_tiles[(size_t)(m / tp->P) * tp->KT + k]; }
-static pb2_data_s* b_tile(pb2_taskpool_s* tp, int k, int n) { return tp->b_tiles[(size_t)(n / tp->Q) * tp->KT + k]; }
+static pb2_data_s* a_tile(pb2_taskpool_s* tp, int m, int k) { return tp->a_tiles[(size_t)tp->row_slot[m] * tp->KT + k]; }
+static pb2_data_s* b_tile(pb2_taskpool_s* tp, int k, int n) { return tp->b_tiles[(size_t)tp->col_slot[n] * tp->KT + k]; }
 
 static int gemm_submit(pb2_device_t* dev, pb2_gpu_task_t* t, void* stream) {
     (void)dev;
@@ -182,10 +185,13 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
     bool types = (tp->gC.mtype == PB2_MATRIX_DOUBLE && tp->gA.mtype == PB2_MATRIX_DOUBLE) ||
                  (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_BF16) ||
                  (tp->gC.mtype == PB2_MATRIX_FLOAT && tp->gA.mtype == PB2_MATRIX_FLOAT);  // fp32 tiles: TF32 tensor cores
-    // the row / column broadcast plan is written for plain cyclic ownership (tile row m on process row m mod P); the
-    // descriptors themselves map k-cyclic layouts exactly as the reference does, and one rank runs them unchanged
-    bool cyclic = tp->gC.P * tp->gC.Q == 1 || (tp->gA.kp == 1 && tp->gA.kq == 1 && tp->gB.kp == 1 && tp->gB.kq == 1 &&
-                                                tp->gC.kp == 1 && tp->gC.kq == 1);
+    // owner-computes with row / column broadcasts: A(m,k) must live in the process row of C(m,n) and B(k,n) in its
+    // process column, i.e. A and C deal tile rows alike, B and C deal tile columns alike, on one grid origin; how the
+    // k dimension is dealt (kq of A, kp of B) is free
+    bool cyclic = tp->gA.kp == tp->gC.kp && tp->gB.kq == tp->gC.kq && tp->gA.ip == tp->gC.ip && tp->gB.ip == tp->gC.ip &&
+                  tp->gA.jq == tp->gC.jq && tp->gB.jq == tp->gC.jq;
+    // sub-matrix views (i, j != 0) shift the ownership of tile (0, 0); only whole matrices on a P x Q grid
+    if (tp->gC.P * tp->gC.Q > 1 && (tp->gA.i || tp->gA.j || tp->gB.i || tp->gB.j || tp->gC.i || tp->gC.j)) cyclic = false;
     if (!ok || !types || !cyclic) {
         delete tp;
         return nullptr;
@@ -194,6 +200,13 @@ extern "C" pb2_taskpool_t* pb2_gemm_taskpool_new(pb2_matrix_block_cyclic_t* A, p
     tp->P = tp->gC.P; tp->Q = tp->gC.Q;
     tp->myrow = tp->gC.rank / tp->Q;
     tp->mycol = tp->gC.rank % tp->Q;
+    int rows = 0, cols = 0;
+    tp->row_slot.assign((size_t)tp->MT, -1);
+    tp->col_slot.assign((size_t)tp->NT, -1);
+    for (int m = 0; m < tp->MT; ++m)
+        if (((m / tp->gC.kp) % tp->P + tp->gC.ip) % tp->P == tp->myrow) tp->row_slot[m] = rows++;
+    for (int n = 0; n < tp->NT; ++n)
+        if (((n / tp->gC.kq) % tp->Q + tp->gC.jq) % tp->Q == tp->mycol) tp->col_slot[n] = cols++;
     return tp;
 }
 
@@ -265,39 +278,44 @@ static int issue_plan_upto(pb2_taskpool_s* tp, int k_limit) {
 }
 
 static int prepare_operands(pb2_taskpool_s* tp) {
-    const int rows = (tp->MT - tp->myrow + tp->P - 1) / tp->P, cols = (tp->NT - tp->mycol + tp->Q - 1) / tp->Q;
-    tp->a_tiles.assign((size_t)std::max(rows, 0) * tp->KT, nullptr);
-    tp->b_tiles.assign((size_t)std::max(cols, 0) * tp->KT, nullptr);
+    int rows = 0, cols = 0;
+    for (int s : tp->row_slot) rows += s >= 0;
+    for (int s : tp->col_slot) cols += s >= 0;
+    tp->a_tiles.assign((size_t)rows * tp->KT, nullptr);
+    tp->b_tiles.assign((size_t)cols * tp->KT, nullptr);
     const uint32_t a_bytes = (uint32_t)((size_t)tp->gA.mb * tp->gA.nb * tp->gA.es);
     const uint32_t b_bytes = (uint32_t)((size_t)tp->gB.mb * tp->gB.nb * tp->gB.es);
-    for (int m = tp->myrow; m < tp->MT; m += tp->P)
-        for (int k = 0; k < tp->KT; ++k) {
+    for (int m = 0; m < tp->MT; ++m)
+        for (int k = 0; k < tp->KT && tp->row_slot[m] >= 0; ++k) {
             pb2_data_s* d = pb2_matrix_data_of(tp->A, m, k);
             if (d) tp->nb_read_a++;  // READ_A(m,k) runs here
             else {
                 d = pb2_data_create(pb2_matrix_data_key(tp->A, m, k), (uint32_t)tp->gA.dc_id, nullptr, a_bytes);
                 tp->proxies.push_back(d);
             }
-            tp->a_tiles[(size_t)(m / tp->P) * tp->KT + k] = d;
+            tp->a_tiles[(size_t)tp->row_slot[m] * tp->KT + k] = d;
         }
-    for (int n = tp->mycol; n < tp->NT; n += tp->Q)
-        for (int k = 0; k < tp->KT; ++k) {
+    for (int n = 0; n < tp->NT; ++n)
+        for (int k = 0; k < tp->KT && tp->col_slot[n] >= 0; ++k) {
             pb2_data_s* d = pb2_matrix_data_of(tp->B, k, n);
             if (d) tp->nb_read_b++;
             else {
                 d = pb2_data_create(pb2_matrix_data_key(tp->B, k, n), (uint32_t)tp->gB.dc_id, nullptr, b_bytes);
                 tp->proxies.push_back(d);
             }
-            tp->b_tiles[(size_t)(n / tp->Q) * tp->KT + k] = d;
+            tp->b_tiles[(size_t)tp->col_slot[n] * tp->KT + k] = d;
         }
     tp->plan.clear();
     tp->plan_pos = 0;
     if (tp->P * tp->Q == 1) return PB2_SUCCESS;
     // READ tasks of tiles that only feed remote GEMMs still execute on their owner: count the owned tiles outside the
     // rows / columns walked above (none on a grid where every rank owns C tiles in each of its rows and columns).
-    int64_t nops = pb2_comm_plan(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, nullptr, 0);
+    int64_t nops = pb2_comm_plan_ex(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, tp->gC.kp, tp->gC.kq, tp->gA.kq,
+                                    tp->gB.kp, tp->gC.ip, tp->gC.jq, nullptr, 0);
+    if (nops < 0) return (int)nops;
     tp->plan.resize((size_t)nops);
-    pb2_comm_plan(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, tp->plan.data(), nops);
+    pb2_comm_plan_ex(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, tp->gC.kp, tp->gC.kq, tp->gA.kq, tp->gB.kp,
+                     tp->gC.ip, tp->gC.jq, tp->plan.data(), nops);
     return issue_plan_upto(tp, tp->bcast_lookahead > 0 ? (int)std::min<int64_t>(tp->bcast_lookahead, tp->KT) : tp->KT);
 }
 

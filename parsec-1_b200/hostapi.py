@@ -216,16 +216,22 @@ class BcastOp(C.Structure):
                 ("i_am_root", C.c_int32)]
 
 
-def comm_plan(P, Q, rank, MT, NT, KT):
-    """pb2_comm_plan: this rank's canonical broadcast sequence as a list of (which, k, idx, root, i_am_root)."""
+def comm_plan(P, Q, rank, MT, NT, KT, kp=1, kq=1, a_kq=1, b_kp=1, ip=0, jq=0):
+    """pb2_comm_plan[_ex]: this rank's canonical broadcast sequence as a list of (which, k, idx, root, i_am_root)."""
     L = lib()
     L.pb2_comm_plan.restype = C.c_int64
     L.pb2_comm_plan.argtypes = [C.c_int] * 6 + [C.c_void_p, C.c_int64]
-    n = L.pb2_comm_plan(P, Q, rank, MT, NT, KT, None, 0)
+    L.pb2_comm_plan_ex.restype = C.c_int64
+    L.pb2_comm_plan_ex.argtypes = [C.c_int] * 12 + [C.c_void_p, C.c_int64]
+    if (kp, kq, a_kq, b_kp, ip, jq) == (1, 1, 1, 1, 0, 0):
+        call = lambda out, cap: L.pb2_comm_plan(P, Q, rank, MT, NT, KT, out, cap)
+    else:
+        call = lambda out, cap: L.pb2_comm_plan_ex(P, Q, rank, MT, NT, KT, kp, kq, a_kq, b_kp, ip, jq, out, cap)
+    n = call(None, 0)
     if n < 0:
         raise ValueError("pb2_comm_plan rejected the arguments (%d)" % n)
     ops = (BcastOp * max(n, 1))()
-    L.pb2_comm_plan(P, Q, rank, MT, NT, KT, ops, n)
+    call(ops, n)
     return [(o.which, o.k, o.idx, o.root, o.i_am_root) for o in ops[:n]]
 
 

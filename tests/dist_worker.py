@@ -16,14 +16,17 @@ def main():
     H = load_hostapi()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     N, NB = int(sys.argv[1]), int(sys.argv[2])
+    # optional: kp kq a_kq b_kp ip jq (k-cyclic super-tiles of C's rows / columns, of k in A / in B, grid origin)
+    kp, kq, a_kq, b_kp, ip, jq = [int(x) for x in sys.argv[3:9]] if len(sys.argv) >= 9 else (1, 1, 1, 1, 0, 0)
+    layouts = ((kp, a_kq), (b_kp, kq), (kp, kq))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     P, Q = H.grid_for(world)
     comm = H.Comm(local, P, Q, rank)
     dev = H.Device(local, memory_number_of_blocks=4096)
     mats, bufs = [], []
-    for seed in (1789, 1805, 1901):
-        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank)
+    for seed, (lr, lc) in zip((1789, 1805, 1901), layouts):
+        m = H.Matrix(H.MATRIX_DOUBLE, N, N, NB, NB, P, Q, rank, kp=lr, kq=lc, ip=ip % P, jq=jq % Q)
         b = torch.zeros(max(m.nbytes, 8), dtype=torch.uint8).pin_memory()
         m.set_buffer(b)
         m.fill_lcg(seed, dev)
@@ -32,21 +35,22 @@ def main():
     for step in range(2):   # twice: the second run finds the owned tiles cached and re-broadcasts the rest
         st = H.tiled_gemm(mats[0], mats[1], mats[2], dev, comm=comm)
     MT = -(-N // NB)
-    owned = sum(1 for n in range(MT) for m in range(MT) if (m % P) * Q + (n % Q) == rank)
+    dl = O.bc(rank, NB, NB, N, N, 0, 0, N, N, P, Q, kp, kq, ip % P, jq % Q)
+    is_mine = lambda m, n: O.lib().orc_bc_rank_of(C.byref(dl), m, n) == rank
+    owned = sum(1 for n in range(MT) for m in range(MT) if is_mine(m, n))
     assert st["nb_gemm"] == owned * MT, (st, owned)
     # oracle: the whole product on one rank, run twice as well; compare my tiles
     d1 = O.square(N, NB)
     A, B, Cm = O.fill(d1, 1789), O.fill(d1, 1805), O.fill(d1, 1901)
     for step in range(2):
         O.tiled_dgemm(N, N, N, NB, NB, NB, A, B, Cm)
-    dl = O.square(N, NB, P, Q, rank)
     mine = bufs[2].numpy().view(np.float64)
     worst = 0.0
     Ad, Bd = O.tiled_to_dense(d1, A), O.tiled_to_dense(d1, B)
     scale = np.abs(Ad).sum(axis=1).max() * np.abs(Bd).sum(axis=1).max() * N * 2.0 ** -53
     for n in range(MT):
         for m in range(MT):
-            if (m % P) * Q + (n % Q) != rank:
+            if not is_mine(m, n):
                 continue
             pl = O.lib().orc_bc_position(C.byref(dl), m, n)
             p1 = O.lib().orc_bc_position(C.byref(d1), m, n)

@@ -74,37 +74,29 @@ def test_descriptor_argument_errors():
     assert not L.pb2_matrix_block_cyclic_new(9, 0, 4, 4, 8, 8, 0, 0, 8, 8, 1, 1, 1, 1, 0, 0)   # unknown mtype
 
 
-def test_k_cyclic_descriptors_map_but_only_plain_cyclic_grids_run_distributed():
-    """kp, kq > 1 are mapped exactly as the reference maps them (tests/test_block_cyclic_golden.py); the P x Q taskpool's
-    broadcast plan is written for plain cyclic ownership, so it takes k-cyclic descriptors on one rank only."""
+def test_taskpool_conformity_of_k_cyclic_descriptors():
+    """Owner-computes with row / column broadcasts needs A and C to deal tile rows alike and B and C tile columns alike,
+    on one grid origin; how the k dimension is dealt is free.  Sub-matrix views are refused on a P x Q grid."""
     L = H.lib()
-    one = [H.Matrix(H.MATRIX_DOUBLE, 64, 64, 8, 8, 1, 1, 0, kp=2, kq=3) for _ in range(3)]
-    tp = L.pb2_gemm_taskpool_new(one[0].h, one[1].h, one[2].h, C.c_void_p(1))   # dev is only stored by _new
-    assert tp
-    L.pb2_gemm_taskpool_free(C.c_void_p(tp))
-    grid = [H.Matrix(H.MATRIX_DOUBLE, 64, 64, 8, 8, 2, 2, 1, kp=2, kq=1) for _ in range(3)]
-    assert not L.pb2_gemm_taskpool_new(grid[0].h, grid[1].h, grid[2].h, C.c_void_p(1))
-    for m in one + grid:
-        m.close()
 
+    def mats(P, Q, rank, a, b, c):
+        return [H.Matrix(H.MATRIX_DOUBLE, 64, 64, 8, 8, P, Q, rank, kp=x[0], kq=x[1], ip=x[2], jq=x[3]) for x in (a, b, c)]
 
-def test_data_master_starts_like_parsec_data_create():
-    L = H.lib()
-    d = C.c_void_p(L.pb2_data_create(42, 7, None, 1024))
-    v = C.c_uint32(99)
-    assert L.pb2_data_copy_version(d, 0, C.byref(v)) == 0 and v.value == 0
-    assert L.pb2_data_copy_coherency(d, 0) == 1       # OWNED
-    assert L.pb2_data_owner_device(d) == 0
-    assert L.pb2_data_copy_coherency(d, 2) == -3      # no copy on the first GPU yet
-    L.pb2_data_destroy(d)
+    def accepted(ms):
+        tp = L.pb2_gemm_taskpool_new(ms[0].h, ms[1].h, ms[2].h, C.c_void_p(1))   # dev is only stored by _new
+        if tp:
+            L.pb2_gemm_taskpool_free(C.c_void_p(tp))
+        for m in ms:
+            m.close()
+        return bool(tp)
 
-
-def test_no_cpu_fallback_without_a_gpu():
-    try:
-        import torch
-        if torch.cuda.is_available():
-            pytest.skip("a CUDA device is present")
-    except ImportError:
-        pass
-    with pytest.raises(RuntimeError, match="no CPU path"):
-        H.Device(0)
+    assert accepted(mats(1, 1, 0, (2, 3, 0, 0), (2, 3, 0, 0), (2, 3, 0, 0)))
+    assert accepted(mats(2, 2, 1, (2, 1, 0, 0), (1, 3, 0, 0), (2, 3, 0, 0)))      # A: kp of C, B: kq of C, k free
+    assert accepted(mats(2, 2, 3, (1, 1, 1, 1), (1, 1, 1, 1), (1, 1, 1, 1)))      # shifted origin, all alike
+    assert not accepted(mats(2, 2, 1, (1, 1, 0, 0), (1, 3, 0, 0), (2, 3, 0, 0)))  # A deals rows unlike C
+    assert not accepted(mats(2, 2, 1, (2, 1, 0, 0), (1, 1, 0, 0), (2, 3, 0, 0)))  # B deals columns unlike C
+    assert not accepted(mats(2, 2, 1, (1, 1, 1, 0), (1, 1, 0, 0), (1, 1, 0, 0)))  # different origins
+    sub = [C.c_void_p(L.pb2_matrix_block_cyclic_new(0, 1, 8, 8, 64, 64, 8, 0, 56, 64, 2, 2, 1, 1, 0, 0)) for _ in range(3)]
+    assert all(sub) and not L.pb2_gemm_taskpool_new(sub[0], sub[1], sub[2], C.c_void_p(1))
+    for m in sub:
+        L.pb2_matrix_block_cyclic_free(m)

@@ -14,37 +14,59 @@ from conftest import load_hostapi
 H = load_hostapi()
 
 
-@pytest.mark.parametrize("P,Q,MT,NT,KT", [(1, 2, 4, 4, 4), (2, 2, 5, 3, 4), (2, 4, 8, 8, 8), (3, 2, 7, 5, 3), (1, 1, 3, 3, 3)])
-def test_plan_is_consistent_across_ranks(P, Q, MT, NT, KT):
-    plans = {r: H.comm_plan(P, Q, r, MT, NT, KT) for r in range(P * Q)}
-    dA = O.bc(0, 1, 1, MT, KT, 0, 0, MT, KT, P, Q)
-    dB = O.bc(0, 1, 1, KT, NT, 0, 0, KT, NT, P, Q)
+# (kp, kq, a_kq, b_kp, ip, jq): k-cyclic super-tiles of C's rows / columns, of the k dimension in A / in B, grid origin
+PLAIN = (1, 1, 1, 1, 0, 0)
+
+
+@pytest.mark.parametrize("P,Q,MT,NT,KT,dist", [
+    (1, 2, 4, 4, 4, PLAIN), (2, 2, 5, 3, 4, PLAIN), (2, 4, 8, 8, 8, PLAIN), (3, 2, 7, 5, 3, PLAIN), (1, 1, 3, 3, 3, PLAIN),
+    (2, 2, 9, 7, 6, (2, 3, 1, 1, 0, 0)), (2, 3, 11, 10, 9, (2, 2, 3, 2, 0, 0)), (3, 2, 10, 9, 8, (3, 1, 2, 2, 1, 1)),
+    (2, 4, 8, 13, 7, (1, 2, 1, 3, 1, 3))])
+def test_plan_is_consistent_across_ranks(P, Q, MT, NT, KT, dist):
+    kp, kq, a_kq, b_kp, ip, jq = dist
+    plans = {r: H.comm_plan(P, Q, r, MT, NT, KT, *dist) for r in range(P * Q)}
+    dA = O.bc(0, 1, 1, MT, KT, 0, 0, MT, KT, P, Q, kp, a_kq, ip, jq)
+    dB = O.bc(0, 1, 1, KT, NT, 0, 0, KT, NT, P, Q, b_kp, kq, ip, jq)
+    dC = O.bc(0, 1, 1, MT, NT, 0, 0, MT, NT, P, Q, kp, kq, ip, jq)
+    rank_of = lambda d, m, n: O.lib().orc_bc_rank_of(C.byref(d), m, n)
     if P * Q == 1:
         assert plans[0] == []
         return
-    # every member of a communicator issues the same sequence on it, exactly one member roots each op, and the root
-    # is the tile's owner under twoDBC_rank_of
+    # every member of a communicator issues the same sequence on it, exactly one member roots each op, the root is the
+    # tile's owner under the reference's rank_of, and a process row moves exactly the A rows of the C tiles it owns
     for row in range(P):
         members = [row * Q + c for c in range(Q)]
         seqs = [[op[:4] for op in plans[r] if op[0] == 0] for r in members]
         assert all(s == seqs[0] for s in seqs)
         if Q > 1:
-            assert sorted((k, m) for (_, k, m, _) in seqs[0]) == [(k, m) for k in range(KT) for m in range(row, MT, P)]
+            mine = [m for m in range(MT) if rank_of(dC, m, 0) // Q == row]
+            assert sorted((k, m) for (_, k, m, _) in seqs[0]) == [(k, m) for k in range(KT) for m in mine]
         for i, (_, k, m, root) in enumerate(seqs[0]):
             roots = [r for r in members if [op for op in plans[r] if op[0] == 0][i][4]]
-            assert roots == [row * Q + root] == [O.lib().orc_bc_rank_of(C.byref(dA), m, k)]
+            assert roots == [row * Q + root] == [rank_of(dA, m, k)]
     for col in range(Q):
         members = [r * Q + col for r in range(P)]
         seqs = [[op[:4] for op in plans[r] if op[0] == 1] for r in members]
         assert all(s == seqs[0] for s in seqs)
         if P > 1:
-            assert sorted((k, n) for (_, k, n, _) in seqs[0]) == [(k, n) for k in range(KT) for n in range(col, NT, Q)]
+            mine = [n for n in range(NT) if rank_of(dC, 0, n) % Q == col]
+            assert sorted((k, n) for (_, k, n, _) in seqs[0]) == [(k, n) for k in range(KT) for n in mine]
         for i, (_, k, n, root) in enumerate(seqs[0]):
             roots = [r for r in members if [op for op in plans[r] if op[0] == 1][i][4]]
-            assert roots == [root * Q + col] == [O.lib().orc_bc_rank_of(C.byref(dB), k, n)]
+            assert roots == [root * Q + col] == [rank_of(dB, k, n)]
     # canonical order inside a rank: k ascending, rows before columns inside a step
     for r, ops in plans.items():
         assert [(k, which) for (which, k, _, _, _) in ops] == sorted((k, which) for (which, k, _, _, _) in ops)
+    # every operand of every GEMM a rank owns is either local or received
+    for r, ops in plans.items():
+        got = {(w, k, i) for (w, k, i, _, _) in ops}
+        for m in range(MT):
+            for n in range(NT):
+                if rank_of(dC, m, n) != r:
+                    continue
+                for k in range(KT):
+                    assert rank_of(dA, m, k) == r or (0, k, m) in got
+                    assert rank_of(dB, k, n) == r or (1, k, n) in got
 
 
 def test_plan_rejects_bad_arguments():
@@ -62,7 +84,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, P, Q, N, NB, out_dir):
+def _worker(rank, world, port, P, Q, N, NB, out_dir, dist_spec):
     import torch
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -70,7 +92,8 @@ def _worker(rank, world, port, P, Q, N, NB, out_dir):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         MT = N // NB
-        descs = [O.square(N, NB, P, Q, rank) for _ in range(3)]
+        kp, kq, a_kq, b_kp, ip, jq = dist_spec
+        descs = [O.bc(rank, NB, NB, N, N, 0, 0, N, N, P, Q, r, c, ip, jq) for (r, c) in ((kp, a_kq), (b_kp, kq), (kp, kq))]
         local = [O.fill(d, s) for d, s in zip(descs, (1789, 1805, 1901))]
         myrow, mycol = rank // Q, rank % Q
         row_group = dist.new_group([myrow * Q + c for c in range(Q)]) if Q > 1 else None
@@ -90,7 +113,7 @@ def _worker(rank, world, port, P, Q, N, NB, out_dir):
             return mat[pos * NB * NB:(pos + 1) * NB * NB]
 
         got = {}
-        for (which, k, idx, root, i_am_root) in H.comm_plan(P, Q, rank, MT, MT, MT):
+        for (which, k, idx, root, i_am_root) in H.comm_plan(P, Q, rank, MT, MT, MT, *dist_spec):
             buf = torch.from_numpy(tile_of(which, idx, k).copy() if which == 0 and i_am_root else
                                    tile_of(which, k, idx).copy() if i_am_root else np.zeros(NB * NB))
             if which == 0:
@@ -122,12 +145,12 @@ def _worker(rank, world, port, P, Q, N, NB, out_dir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1)])
-def test_two_gloo_ranks_reproduce_the_single_rank_result(tmp_path, P, Q):
+@pytest.mark.parametrize("P,Q,dist_spec", [(1, 2, PLAIN), (2, 1, PLAIN), (1, 2, (1, 2, 2, 1, 0, 1)), (2, 1, (2, 1, 1, 2, 1, 0))])
+def test_two_gloo_ranks_reproduce_the_single_rank_result(tmp_path, P, Q, dist_spec):
     import torch.multiprocessing as mp
-    N, NB = 256, 64
+    N, NB = 384, 64
     port = _free_port()
-    mp.spawn(_worker, args=(2, port, P, Q, N, NB, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, port, P, Q, N, NB, str(tmp_path), dist_spec), nprocs=2, join=True)
     d = O.square(N, NB)
     A, B, Cm = O.fill(d, 1789), O.fill(d, 1805), O.fill(d, 1901)
     O.tiled_dgemm(N, N, N, NB, NB, NB, A, B, Cm)
