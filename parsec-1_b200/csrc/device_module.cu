@@ -74,7 +74,7 @@ struct pb2_device_s {
     int next_exec = 0;
     int active_exec = 0;  // exec streams the last task was spread over (see try_submit)
     uint64_t h2d_seq = 0;  // number of push events recorded so far
-    cudaEvent_t h2d_events[pb2::EVENT_RING];
+    cudaEvent_t h2d_events[pb2::EVENT_RING] = {};
     std::vector<cudaEvent_t> event_pool;
     // in flight, one FIFO per stream that carries the final event: exec streams, then d2h, then h2d (prefetches).
     // Events of one stream complete in order, so only the heads are ever polled.
@@ -168,20 +168,34 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
         d->device_index = idx;
         g_devices[idx] = d;
     }
+    // from here on a failure tears down whatever exists (streams, events, the slot in g_devices)
+    auto fail = [d](cudaError_t e, int line) {
+        fprintf(stderr, "[parsec_b200] CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, line);
+        pb2_device_destroy(d);
+        return PB2_ERR_DEVICE;
+    };
+    cudaError_t ce;
     int nexec = std::max(1, d->params.max_streams - 2);
-    PB2_CUDA_OK(cudaStreamCreateWithFlags(&d->h2d, cudaStreamNonBlocking));
-    PB2_CUDA_OK(cudaStreamCreateWithFlags(&d->d2h, cudaStreamNonBlocking));
-    d->exec.resize(nexec);
+    d->exec.assign(nexec, nullptr);
     d->exec_waited_seq.assign(nexec, 0);
     d->launch_marks.resize(nexec);
     d->inflight_q.resize(nexec + 2);
-    for (int i = 0; i < nexec; ++i) PB2_CUDA_OK(cudaStreamCreateWithFlags(&d->exec[i], cudaStreamNonBlocking));
-    for (int i = 0; i < EVENT_RING; ++i) PB2_CUDA_OK(cudaEventCreateWithFlags(&d->h2d_events[i], cudaEventDisableTiming));
+    if ((ce = cudaStreamCreateWithFlags(&d->h2d, cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, __LINE__);
+    if ((ce = cudaStreamCreateWithFlags(&d->d2h, cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, __LINE__);
+    for (int i = 0; i < nexec; ++i)
+        if ((ce = cudaStreamCreateWithFlags(&d->exec[i], cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, __LINE__);
+    for (int i = 0; i < EVENT_RING; ++i)
+        if ((ce = cudaEventCreateWithFlags(&d->h2d_events[i], cudaEventDisableTiming)) != cudaSuccess) return fail(ce, __LINE__);
 
     // parsec_cuda_memory_reserve (:612-743): one allocation, carved in memory_block_size units
     size_t unit = (size_t)d->params.memory_block_size;
     size_t free_b = 0, total_b = 0;
-    PB2_CUDA_OK(cudaMemGetInfo(&free_b, &total_b));
+    if (unit == 0) {
+        fprintf(stderr, "[parsec_b200] memory_block_size must be positive\n");
+        pb2_device_destroy(d);
+        return PB2_ERR_BAD_PARAM;
+    }
+    if ((ce = cudaMemGetInfo(&free_b, &total_b)) != cudaSuccess) return fail(ce, __LINE__);
     size_t want;
     if (d->params.memory_number_of_blocks > 0) want = (size_t)d->params.memory_number_of_blocks * unit;
     else want = (size_t)((double)free_b * d->params.memory_use_percent / 100.0);
@@ -189,10 +203,12 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
     while (nblocks > 0) {
         if (cudaMalloc((void**)&d->hbm_base, nblocks * unit) == cudaSuccess) break;
         cudaGetLastError();
+        d->hbm_base = nullptr;
         nblocks -= std::max<size_t>(1, nblocks / 64);
     }
     if (!nblocks || !d->hbm_base) {
         fprintf(stderr, "[parsec_b200] cannot reserve device memory\n");
+        pb2_device_destroy(d);
         return PB2_ERR_OUT_OF_RESOURCE;
     }
     d->heap = new ZoneHeap(d->hbm_base, (int)nblocks, unit);
@@ -231,10 +247,12 @@ extern "C" int pb2_device_destroy(pb2_device_t* d) {
     while (pb2_copy_t* c = d->owned_lru.pop_front()) release_copy(d, c);
     pb2_device_free_workspace(d);
     for (auto& kv : d->registered) cudaHostUnregister(kv.first);
-    for (cudaStream_t s : d->exec) cudaStreamDestroy(s);
-    cudaStreamDestroy(d->h2d);
-    cudaStreamDestroy(d->d2h);
-    for (int i = 0; i < EVENT_RING; ++i) cudaEventDestroy(d->h2d_events[i]);
+    for (cudaStream_t s : d->exec)
+        if (s) cudaStreamDestroy(s);
+    if (d->h2d) cudaStreamDestroy(d->h2d);
+    if (d->d2h) cudaStreamDestroy(d->d2h);
+    for (int i = 0; i < EVENT_RING; ++i)
+        if (d->h2d_events[i]) cudaEventDestroy(d->h2d_events[i]);
     for (cudaEvent_t e : d->event_pool) cudaEventDestroy(e);
     if (d->hbm_base) cudaFree(d->hbm_base);
     delete d->heap;
@@ -673,7 +691,11 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t) {
     // records the state right after it.
 }
 
-static bool progress_completions(pb2_device_s* d) {
+// *drained is set by the decrement that takes the task count to zero.  From that instant the next caller of
+// pb2_kernel_scheduler sees rc == 0 and is the manager (:2573-2589), so this thread must not touch the module's state
+// any more: it returns at once and manager_loop leaves without looking at anything again, exactly like the reference's
+// `rc = fetch_dec(mutex); if (1 == rc) leave` (:2742-2753).  Re-reading the counter instead would let two managers run.
+static bool progress_completions(pb2_device_s* d, bool* drained) {
     bool any = false;
     for (auto& queue : d->inflight_q) {
         while (!queue.empty()) {
@@ -702,7 +724,10 @@ static bool progress_completions(pb2_device_s* d) {
                 for (int i = 0; i < t->nb_flows; ++i)
                     if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && t->flow_data[i]) trace(d, t, i, EV_COMPLETE, 0);
             free(t);
-            d->mutex.fetch_sub(1);
+            if (d->mutex.fetch_sub(1) == 1) {
+                *drained = true;
+                return true;
+            }
         }
     }
     return any;
@@ -752,6 +777,8 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
     const size_t max_inflight = (size_t)std::max(1, d->params.max_inflight_tasks);
     uint64_t idle_spins = 0;
     int burst = 0;  // submissions since the completion queues were last polled
+    bool drained = false;
+    const auto leave = [d]() { return d->failed ? PB2_HOOK_RETURN_DISABLE : PB2_HOOK_RETURN_ASYNC; };
     while (true) {
         bool progressed = false;
         // 1. stalled tasks go first (they hold the oldest priorities), then the new one
@@ -807,14 +834,15 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
                     d->failed = true;
                     if (cur->complete) cur->complete(cur, PB2_HOOK_RETURN_ERROR, cur->complete_cookie);
                     free(cur);
-                    d->mutex.fetch_sub(1);
+                    if (d->mutex.fetch_sub(1) == 1) return leave();
                     cur = nullptr;
                 } else {
                     d->stalled.push_front(cur);
                     cur = nullptr;
                     // block until something completes, otherwise we would spin on the same failure
-                    while (!progress_completions(d)) {
+                    while (!progress_completions(d, &drained)) {
                     }
+                    if (drained) return leave();
                     progressed = true;
                 }
             } else {
@@ -825,7 +853,7 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
                 }
                 if (cur->complete) cur->complete(cur, r, cur->complete_cookie);
                 free(cur);
-                d->mutex.fetch_sub(1);
+                if (d->mutex.fetch_sub(1) == 1) return leave();
                 cur = nullptr;
             }
         }
@@ -833,15 +861,16 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
         burst = 0;
         {
             auto tr0 = std::chrono::steady_clock::now();
-            bool any = progress_completions(d);
+            bool any = progress_completions(d, &drained);
+            if (drained) return leave();
             if (any) {
                 progressed = true;
                 d->stats.host_retire_ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
                                                std::chrono::steady_clock::now() - tr0).count();
             }
         }
-        // 3. leave when the device is drained (:2742-2753)
-        if (d->mutex.load() == 0) break;
+        // 3. the device drains inside progress_completions (the decrement that reaches zero), never by re-reading the
+        //    counter here: see the comment there
         if (!progressed) {
             if (++idle_spins > 64 && d->inflight_count == 0 && d->stalled.empty()) {
                 // tasks counted in mutex but not yet visible in pending (a submitter between its two steps)

@@ -15,10 +15,15 @@ pytestmark = pytest.mark.gpu
 H = load_hostapi()
 
 
-def test_four_threads_submit_concurrently():
+@pytest.mark.parametrize("pause_us", [0, 150])
+def test_four_threads_submit_concurrently(pause_us):
+    """pause_us = 0: one manager mostly drives everything.  With a pause between a thread's submissions the device keeps
+    draining, so the manager seat changes hands over and over: the decrement that empties the module and the next
+    caller's increment race for real (the outgoing manager must not touch the module after that decrement)."""
+    import time
     import torch
     L = H.lib()
-    NB, PER_THREAD, THREADS = 64, 48, 4
+    NB, PER_THREAD, THREADS = 64, 48 if pause_us == 0 else 160, 4
     total = PER_THREAD * THREADS
     tile_bytes = NB * NB * 8
     dev = H.Device(0, memory_block_size=64 * 1024, memory_number_of_blocks=1024)
@@ -62,6 +67,8 @@ def test_four_threads_submit_concurrently():
                 t.complete = complete
                 t.locals[0] = i
                 rcs.append(L.pb2_kernel_scheduler(dev.h, raw))
+                if pause_us:
+                    time.sleep(pause_us * 1e-6 * (1 + (i * 7919) % 5))
 
         threads = [threading.Thread(target=worker, args=(w,)) for w in range(THREADS)]
         for th in threads:
@@ -72,6 +79,8 @@ def test_four_threads_submit_concurrently():
         assert rcs == [H.HOOK_RETURN_ASYNC] * total
         assert sorted(done) == [(i, 0) for i in range(total)]
         assert len(managers) >= 1
+        if pause_us:
+            print("manager seat held by %d different threads" % len(managers))
         assert dev.stats()["executed_tasks"] == total
         for i in range(total):
             a = before[i * NB * NB:(i + 1) * NB * NB].reshape((NB, NB), order="F")
