@@ -79,6 +79,13 @@ extern "C" int pb2_comm_unique_id(void* out128) {
     return PB2_SUCCESS;
 }
 
+static void comm_free(pb2_comm_s* c) {  // whatever exists of a communicator (also the failure paths of pb2_comm_create)
+    if (c->row) nccl_api()->CommDestroy(c->row);
+    if (c->col) nccl_api()->CommDestroy(c->col);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
 // row_id: the unique id published by the rank in column 0 of my process row; col_id: by the rank in row 0 of my column.
 extern "C" int pb2_comm_create(int cuda_index, int P, int Q, int rank, const void* row_id, const void* col_id,
                                pb2_comm_t** out) {
@@ -92,17 +99,17 @@ extern "C" int pb2_comm_create(int cuda_index, int P, int Q, int rank, const voi
     // SM slots behind them turns the data plane into the critical path
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { delete c; return PB2_ERR_DEVICE; }
+    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
     ncclUniqueId rid, cid;
     if (Q > 1) {
-        if (!row_id) { delete c; return PB2_ERR_BAD_PARAM; }
+        if (!row_id) { comm_free(c); return PB2_ERR_BAD_PARAM; }
         memcpy(&rid, row_id, 128);
-        if (nccl->CommInitRank(&c->row, Q, rid, c->mycol) != ncclSuccess) { delete c; return PB2_ERR_DEVICE; }
+        if (nccl->CommInitRank(&c->row, Q, rid, c->mycol) != ncclSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
     }
     if (P > 1) {
-        if (!col_id) { delete c; return PB2_ERR_BAD_PARAM; }
+        if (!col_id) { comm_free(c); return PB2_ERR_BAD_PARAM; }
         memcpy(&cid, col_id, 128);
-        if (nccl->CommInitRank(&c->col, P, cid, c->myrow) != ncclSuccess) { delete c; return PB2_ERR_DEVICE; }
+        if (nccl->CommInitRank(&c->col, P, cid, c->myrow) != ncclSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
     }
     *out = c;
     return PB2_SUCCESS;
@@ -112,10 +119,7 @@ extern "C" int pb2_comm_destroy(pb2_comm_t* c) {
     if (!c) return PB2_ERR_BAD_PARAM;
     cudaSetDevice(c->cuda_index);
     cudaStreamSynchronize(c->stream);
-    if (c->row) nccl_api()->CommDestroy(c->row);
-    if (c->col) nccl_api()->CommDestroy(c->col);
-    cudaStreamDestroy(c->stream);
-    delete c;
+    comm_free(c);
     return PB2_SUCCESS;
 }
 
