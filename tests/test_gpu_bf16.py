@@ -30,12 +30,19 @@ def _run(m, n, k, alpha, beta, seed=0, ld_pad=0, ldc_extra=0):
         buf[:, :X.shape[0]] = X.T
         return torch.from_numpy(buf.view(np.int16) if dtype == np.uint16 else buf).cuda()
 
-    dA, dB, dC = to_dev(A, lda, np.uint16), to_dev(B, ldb, np.uint16), to_dev(Cm, ldc, np.float32)
+    # C sits between guard columns (4 on each side keep its base 16-byte aligned whenever ldc % 4 == 0, so the TMA
+    # epilogue is exercised) and its leading-dimension padding holds a canary: only the m x n elements may change
+    CANARY, G = np.float32(12345.0), 4
+    hostC = np.full((n + 2 * G, ldc), CANARY, dtype=np.float32)
+    hostC[G:n + G, :m] = Cm.T
+    dA, dB, dCg = to_dev(A, lda, np.uint16), to_dev(B, ldb, np.uint16), torch.from_numpy(hostC).cuda()
     rc = H.lib().parsec_b200_gemm_bf16_sm100(b"N", b"N", m, n, k, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta,
-                                              dC.data_ptr(), ldc, torch.cuda.current_stream().cuda_stream)
+                                              dCg.data_ptr() + 4 * G * ldc, ldc, torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     torch.cuda.synchronize()
-    got = dC.cpu().numpy()[:, :m].T
+    back = dCg.cpu().numpy()
+    assert np.all(back[:G] == CANARY) and np.all(back[n + G:] == CANARY) and np.all(back[G:n + G, m:] == CANARY)
+    got = back[G:n + G, :m].T
     want = Cm.copy(order="F")
     O.lib().orc_gemm_tile_bf16(m, n, k, alpha, A.ctypes.data, m, B.ctypes.data, k, beta, want.ctypes.data, m)
     back = lambda X: (X.astype(np.uint32) << 16).view(np.float32).astype(np.float64)

@@ -25,12 +25,19 @@ def _run(transa, transb, m, n, k, alpha, beta, seed=0, lda_pad=0):
         buf[:, :X.shape[0]] = X.T
         return torch.from_numpy(buf).cuda()
 
-    dA, dB, dC = to_dev(A, lda), to_dev(B, ldb), to_dev(Cm, ldc)
-    rc = H.dgemm(transa, transb, m, n, k, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dC.data_ptr(), ldc,
+    # C sits between two guard columns and its leading-dimension padding holds a canary: the kernel may write the
+    # m x n elements of C and nothing else (compute-sanitizer is not available on the GPU pool)
+    CANARY = 12345.0
+    hostC = np.full((n + 2, ldc), CANARY)
+    hostC[1:n + 1, :m] = Cm.T
+    dA, dB, dCg = to_dev(A, lda), to_dev(B, ldb), torch.from_numpy(hostC).cuda()
+    rc = H.dgemm(transa, transb, m, n, k, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dCg.data_ptr() + 8 * ldc, ldc,
                  torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     torch.cuda.synchronize()
-    got = dC.cpu().numpy()[:, :m].T
+    back = dCg.cpu().numpy()
+    assert np.all(back[0] == CANARY) and np.all(back[n + 1] == CANARY) and np.all(back[1:n + 1, m:] == CANARY)
+    got = back[1:n + 1, :m].T
     want = np.asfortranarray(Cm.copy())
     O.dgemm_tile(alpha, np.asfortranarray(opA), np.asfortranarray(opB), beta, want)
     # north-star norm with N := k (the contraction length of this tile product)
