@@ -10,6 +10,7 @@ size-independent properties because the oracle's O(N^3) DGEMM would take hours h
 import numpy as np
 import pytest
 
+import oracle_lib as O
 from conftest import load_hostapi
 
 pytestmark = pytest.mark.gpu
@@ -59,6 +60,9 @@ def test_config2_full_size_freivalds_counts_and_versions():
         rng = np.random.default_rng(11)
         x = rng.integers(0, 2, N).astype(np.float64) * 2.0 - 1.0
         c0x = _matvec_tiled(bufs[2], x, T, T, NB)
+        sampled = [(0, 0), (T - 1, T - 2), (T // 2, T - 1)]     # C tiles recomputed on the host cores after the run
+        tile_of = lambda b, m, n: b.numpy().view(np.float64)[(n * T + m) * NB * NB:(n * T + m + 1) * NB * NB]
+        c_before = {mn: tile_of(bufs[2], *mn).reshape((NB, NB), order="F").copy(order="F") for mn in sampled}
         dev.stats(reset=True)
         st = H.tiled_gemm(mats[0], mats[1], mats[2], dev)
         s = dev.stats()
@@ -77,6 +81,23 @@ def test_config2_full_size_freivalds_counts_and_versions():
         assert np.max(np.abs(c1x - c0x - abx)) / denom < 10
         # the run really changed C (a no-op pipeline would pass a weaker check)
         assert np.max(np.abs(c1x - c0x)) > 1.0
+        # sampled tiles: the chain C(m,n) += A(m,k) B(k,n), k ascending, recomputed tile by tile -- the
+        # first with the oracle's tile GEMM, the others with numpy -- against what the pipeline wrote back
+        inf = lambda X: np.abs(X).sum(axis=1).max()
+        for idx, (m, n) in enumerate(sampled):
+            want = c_before[(m, n)]
+            a_row = b_col = 0.0
+            for k in range(T):
+                a = np.asfortranarray(tile_of(bufs[0], m, k).reshape((NB, NB), order="F"))
+                b = np.asfortranarray(tile_of(bufs[1], k, n).reshape((NB, NB), order="F"))
+                if idx == 0:
+                    O.dgemm_tile(1.0, a, b, 1.0, want)
+                else:
+                    want += a @ b
+                a_row, b_col = a_row + np.abs(a).sum(axis=1), b_col + np.abs(b).sum(axis=0)
+            got = tile_of(bufs[2], m, n).reshape((NB, NB), order="F")
+            # row-wise forward bound of the inner products: |err_ij| <= N eps sum_k |a_ik| |b_kj|
+            assert inf(got - want) / (a_row.max() * b_col.max() * N * eps) < 10
     finally:
         for m in mats:
             m.close()
