@@ -98,6 +98,13 @@ typedef struct pb2_device_s pb2_device_t; /* parsec_device_cuda_module_t */
 
 /* parsec_data_create (parsec/data.c:484-522): one host copy, coherency OWNED, version 0, owner device 0. */
 pb2_data_t* pb2_data_create(uint64_t key, uint32_t dc_id, void* host_ptr, uint32_t nb_elts);
+/* The host tile is a window of a larger column-major matrix (the job of the user stage functions of
+ * tests/dsl/ptg/cuda/stage_custom.jdf:28-109, which read dc->llm): `height` columns of `width_bytes`, `host_pitch_bytes`
+ * apart on the host and `dev_pitch_bytes` apart in the packed device tile (dev_pitch_bytes * height <= nb_elts).  The
+ * default stage-in / stage-out and the write-back of evicted tiles then use pitched 2D copies.  host_pitch_bytes = 0
+ * restores the packed layout.  pb2_matrix_block_cyclic_lapack_new sets this on the tiles it creates. */
+int pb2_data_set_host_layout(pb2_data_t* data, uint32_t width_bytes, uint32_t height, size_t host_pitch_bytes,
+                             size_t dev_pitch_bytes);
 /* parsec_data_destroy (parsec/data.c) -- detaches device copies first. */
 void pb2_data_destroy(pb2_data_t* data);
 /* field readers used by tests / shims: parsec_data_copy_t.version, .coherency_state, .readers, parsec_data_t.owner_device */
@@ -247,6 +254,15 @@ typedef struct pb2_matrix_block_cyclic_s pb2_matrix_block_cyclic_t;
 pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int myrank, int mb, int nb, int lm, int ln, int i,
                                                        int j, int m, int n, int P, int Q, int kp, int kq, int ip,
                                                        int jq);
+/* parsec_matrix_block_cyclic_lapack_init (two_dim_rectangle_cyclic.c:61-107): PARSEC_MATRIX_LAPACK storage.  dc->mat is
+ * a column-major local matrix of mloc x nloc elements (ld = mloc), not padded to whole tiles; a tile is a window of
+ * it.  The device copy of a tile stays packed (ld = mb): the module's default stage-in / stage-out and its write-back
+ * of evicted tiles move such tiles with pitched 2D copies, so no custom stage functions are needed (what
+ * tests/dsl/ptg/cuda/stage_custom.jdf:28-109 does by hand), and short edge tiles move only the rows and columns the
+ * matrix has.  pb2_matrix_fill_lcg* do not support this storage. */
+pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_lapack_new(int mtype, int myrank, int mb, int nb, int lm, int ln,
+                                                              int i, int j, int m, int n, int P, int Q, int kp, int kq,
+                                                              int ip, int jq, int mloc, int nloc);
 void pb2_matrix_block_cyclic_free(pb2_matrix_block_cyclic_t* dc);
 /* dc->mat = user memory holding nb_local_tiles * mb * nb elements */
 int pb2_matrix_set_mat(pb2_matrix_block_cyclic_t* dc, void* mat);
@@ -258,6 +274,9 @@ int pb2_matrix_nt(const pb2_matrix_block_cyclic_t* dc);
 int pb2_matrix_rank_of(const pb2_matrix_block_cyclic_t* dc, int m, int n);
 int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int m, int n);
 uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n);
+/* element offset of tile (m, n) from dc->mat, either storage: position * mb * nb, or (local_m * mb) + (local_n * nb) *
+ * mloc for LAPACK storage (twoDBC_data_of :397-411) */
+int64_t pb2_matrix_tile_offset(const pb2_matrix_block_cyclic_t* dc, int m, int n);
 pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, int n);
 /* twoDBC_memory_register (:39-49) -> pb2_device_memory_register over the local matrix */
 int pb2_matrix_register_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev);

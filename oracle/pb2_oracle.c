@@ -91,6 +91,30 @@ void orc_bc_init(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i
     dc->lln = dc->nb_elem_c * nb;
 }
 
+/* parsec_matrix_block_cyclic_lapack_init (two_dim_rectangle_cyclic.c:61-107): the block-cyclic init with
+ * PARSEC_MATRIX_LAPACK storage -- lm / ln are NOT padded to whole tiles (matrix.c:103-107) -- and then llm / lln
+ * overwritten with the local matrix size the caller gives. */
+void orc_bc_init_lapack(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P,
+                        int Q, int kp, int kq, int ip, int jq, int mloc, int nloc) {
+    orc_bc_init(dc, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq);
+    dc->lm = lm;
+    dc->ln = ln;
+    dc->llm = mloc;
+    dc->lln = nloc;
+    dc->lapack = 1;
+}
+
+/* twoDBC_data_of (:397-411) / twoDBC_kcyclic_data_of (:666-675): tile storage puts tile `position` at position * bsiz;
+ * LAPACK storage addresses element (local_m * mb, local_n * nb) of the column-major local matrix with ld = llm. */
+int64_t orc_bc_offset(const orc_bc_t* dc, int m, int n) {
+    if (!dc->lapack) return (int64_t)orc_bc_position(dc, m, n) * dc->bsiz;
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    int64_t local_m = (m / (dc->kp * dc->P)) * dc->kp + (m % (dc->kp * dc->P)) % dc->kp;
+    int64_t local_n = (n / (dc->kq * dc->Q)) * dc->kq + (n % (dc->kq * dc->Q)) % dc->kq;
+    return local_n * dc->nb * dc->llm + local_m * dc->mb;
+}
+
 int orc_bc_rank_of(const orc_bc_t* dc, int m, int n) {
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;

@@ -42,11 +42,17 @@ typedef struct orc_bc_s {
     int mt, nt, lmt, lnt, llm, lln, bsiz;
     int P, Q, kp, kq, ip, jq, rrank, crank, myrank;
     int nb_elem_r, nb_elem_c, nb_local_tiles;
+    int lapack; /* 0 = PARSEC_MATRIX_TILE storage, 1 = PARSEC_MATRIX_LAPACK (column-major local matrix, ld = llm) */
 } orc_bc_t;
 
 void orc_bc_init(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q,
                  int kp, int kq, int ip, int jq);
+/* parsec_matrix_block_cyclic_lapack_init: LAPACK storage, the caller says how large the local matrix is (mloc x nloc) */
+void orc_bc_init_lapack(orc_bc_t* dc, int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P,
+                        int Q, int kp, int kq, int ip, int jq, int mloc, int nloc);
 int orc_bc_rank_of(const orc_bc_t* dc, int m, int n);
+/* element offset of tile (m, n) inside the local matrix (what data_of adds to dc->mat), either storage */
+int64_t orc_bc_offset(const orc_bc_t* dc, int m, int n);
 int orc_bc_position(const orc_bc_t* dc, int m, int n);
 uint64_t orc_bc_key(const orc_bc_t* dc, int m, int n);
 uint64_t orc_bc_data_of_key(const orc_bc_t* dc, int m, int n); /* key of the parsec_data_t data_of creates */

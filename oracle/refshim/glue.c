@@ -90,6 +90,13 @@ void* ref_bc_new(int myrank, int mb, int nb, int lm, int ln, int i, int j, int m
                                     kp, kq, ip, jq);
     return dc;
 }
+void* ref_bc_lapack_new(int myrank, int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q, int kp,
+                        int kq, int ip, int jq, int mloc, int nloc) {
+    parsec_matrix_block_cyclic_t* dc = (parsec_matrix_block_cyclic_t*)calloc(1, sizeof(*dc));
+    parsec_matrix_block_cyclic_lapack_init(dc, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, myrank, mb, nb, lm, ln, i, j, m, n,
+                                           P, Q, kp, kq, ip, jq, mloc, nloc);
+    return dc;
+}
 /* out: mt, nt, lmt, lnt, lm, ln, llm, lln, bsiz, nb_elem_r, nb_elem_c, nb_local_tiles, rrank, crank */
 void ref_bc_geometry(void* p, int* out) {
     parsec_matrix_block_cyclic_t* dc = (parsec_matrix_block_cyclic_t*)p;

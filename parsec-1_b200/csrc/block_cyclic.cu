@@ -15,6 +15,7 @@ struct pb2_matrix_block_cyclic_s {
     int mb, nb, lm, ln, i, j, m, n, mt, nt, lmt, lnt, llm, lln, bsiz;
     int P, Q, kp, kq, ip, jq, rrank, crank, myrank;
     int nb_elem_r, nb_elem_c;
+    int lapack = 0;  // 0 = PARSEC_MATRIX_TILE storage, 1 = PARSEC_MATRIX_LAPACK (column-major local matrix, ld = llm)
     int64_t nb_local_tiles;
     void* mat;
     uint32_t dc_id;
@@ -30,9 +31,9 @@ static int owned_along(int first_block, int k, int procs, int total) {
     return have;
 }
 
-extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int myrank, int mb, int nb, int lm,
-                                                                  int ln, int i, int j, int m, int n, int P, int Q,
-                                                                  int kp, int kq, int ip, int jq) {
+static pb2_matrix_block_cyclic_t* make_descriptor(int mtype, int myrank, int mb, int nb, int lm, int ln, int i, int j, int m,
+                                                  int n, int P, int Q, int kp, int kq, int ip, int jq, int lapack, int mloc,
+                                                  int nloc) {
     if (mb <= 0 || nb <= 0 || lm <= 0 || ln <= 0 || m <= 0 || n <= 0 || P <= 0 || Q <= 0 || kp <= 0 || kq <= 0 ||
         myrank < 0 || myrank >= P * Q || i < 0 || j < 0 || i + m > lm || j + n > ln)
         return nullptr;
@@ -44,8 +45,10 @@ extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int
     dc->mb = mb; dc->nb = nb; dc->bsiz = mb * nb;
     dc->lmt = (lm + mb - 1) / mb;
     dc->lnt = (ln + nb - 1) / nb;
-    dc->lm = dc->lmt * mb;
-    dc->ln = dc->lnt * nb;
+    // tile storage pads the matrix to whole tiles, LAPACK storage does not (matrix.c:103-107)
+    dc->lm = lapack ? lm : dc->lmt * mb;
+    dc->ln = lapack ? ln : dc->lnt * nb;
+    dc->lapack = lapack;
     dc->i = i; dc->j = j; dc->m = m; dc->n = n;
     dc->mt = (i + m - 1) / mb - i / mb + 1;
     dc->nt = (j + n - 1) / nb - j / nb + 1;
@@ -59,10 +62,28 @@ extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int
     dc->nb_local_tiles = (int64_t)dc->nb_elem_r * dc->nb_elem_c;
     dc->llm = dc->nb_elem_r * mb;
     dc->lln = dc->nb_elem_c * nb;
+    if (lapack) {  // parsec_matrix_block_cyclic_lapack_init (:61-107): the caller says how large the local matrix is
+        dc->llm = mloc;
+        dc->lln = nloc;
+    }
     dc->mat = nullptr;
     dc->dc_id = g_next_dc_id.fetch_add(1);
     dc->data_map.assign((size_t)dc->nb_local_tiles, nullptr);
     return dc;
+}
+
+extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_new(int mtype, int myrank, int mb, int nb, int lm,
+                                                                  int ln, int i, int j, int m, int n, int P, int Q,
+                                                                  int kp, int kq, int ip, int jq) {
+    return make_descriptor(mtype, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq, 0, 0, 0);
+}
+
+extern "C" pb2_matrix_block_cyclic_t* pb2_matrix_block_cyclic_lapack_new(int mtype, int myrank, int mb, int nb, int lm,
+                                                                         int ln, int i, int j, int m, int n, int P,
+                                                                         int Q, int kp, int kq, int ip, int jq,
+                                                                         int mloc, int nloc) {
+    if (mloc <= 0 || nloc <= 0) return nullptr;
+    return make_descriptor(mtype, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq, 1, mloc, nloc);
 }
 
 extern "C" void pb2_matrix_block_cyclic_free(pb2_matrix_block_cyclic_t* dc) {
@@ -100,6 +121,19 @@ extern "C" int64_t pb2_matrix_position(const pb2_matrix_block_cyclic_t* dc, int 
     return (int64_t)dc->nb_elem_r * local_n + local_m;
 }
 
+// Element offset of tile (m, n) inside the local matrix, what data_of adds to dc->mat: tile storage keeps tile
+// `position` at position * bsiz (:397-401); LAPACK storage addresses element (local_m * mb, local_n * nb) of the
+// column-major local matrix with ld = llm (:402-407, :666-675).
+extern "C" int64_t pb2_matrix_tile_offset(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
+    if (!dc || m < 0 || n < 0 || m >= dc->mt || n >= dc->nt) return PB2_ERR_BAD_PARAM;
+    if (!dc->lapack) return pb2_matrix_position(dc, m, n) * dc->bsiz;
+    m += dc->i / dc->mb;
+    n += dc->j / dc->nb;
+    const int64_t local_m = (m / (dc->kp * dc->P)) * dc->kp + (m % (dc->kp * dc->P)) % dc->kp;
+    const int64_t local_n = (n / (dc->kq * dc->Q)) * dc->kq + (n % (dc->kq * dc->Q)) % dc->kq;
+    return local_n * dc->nb * dc->llm + local_m * dc->mb;
+}
+
 extern "C" uint64_t pb2_matrix_data_key(const pb2_matrix_block_cyclic_t* dc, int m, int n) {
     m += dc->i / dc->mb;
     n += dc->j / dc->nb;
@@ -111,7 +145,7 @@ extern "C" pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, 
     int64_t pos = pb2_matrix_position(dc, m, n);
     std::lock_guard<std::mutex> g(dc->lock);
     if (!dc->data_map[(size_t)pos]) {
-        char* ptr = dc->mat ? (char*)dc->mat + (size_t)pos * dc->bsiz * dc->elem_size : nullptr;
+        char* ptr = dc->mat ? (char*)dc->mat + (size_t)pb2_matrix_tile_offset(dc, m, n) * dc->elem_size : nullptr;
         // key of the parsec_data_t: the data key, except that twoDBC_kcyclic_data_of builds it from the coordinates it
         // has just reduced modulo the super-tile period (:652-678); kept as the reference has it
         uint64_t key = pb2_matrix_data_key(dc, m, n);
@@ -119,14 +153,24 @@ extern "C" pb2_data_t* pb2_matrix_data_of(pb2_matrix_block_cyclic_t* dc, int m, 
             const int gm = (m + dc->i / dc->mb) % (dc->kp * dc->P), gn = (n + dc->j / dc->nb) % (dc->kq * dc->Q);
             key = (uint64_t)gn * (uint64_t)dc->lmt + (uint64_t)gm;
         }
-        dc->data_map[(size_t)pos] = pb2_data_create(key, dc->dc_id, ptr, (uint32_t)((size_t)dc->bsiz * dc->elem_size));
+        pb2_data_s* d = pb2_data_create(key, dc->dc_id, ptr, (uint32_t)((size_t)dc->bsiz * dc->elem_size));
+        if (d && dc->lapack) {
+            // a window of the local matrix: only the rows / columns the matrix really has (the last tile row / column of
+            // an unpadded matrix is short; the reference's stage_custom functions copy mb x nb regardless and need N % NB == 0)
+            const int gm = m + dc->i / dc->mb, gn = n + dc->j / dc->nb;
+            const int rows = std::min(dc->mb, dc->lm - gm * dc->mb), cols = std::min(dc->nb, dc->ln - gn * dc->nb);
+            pb2_data_set_host_layout(d, (uint32_t)(rows * dc->elem_size), (uint32_t)cols, (size_t)dc->llm * dc->elem_size,
+                                     (size_t)dc->mb * dc->elem_size);
+        }
+        dc->data_map[(size_t)pos] = d;
     }
     return dc->data_map[(size_t)pos];
 }
 
 extern "C" int pb2_matrix_register_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev) {
     if (!dc || !dev || !dc->mat) return PB2_ERR_BAD_PARAM;
-    return pb2_device_memory_register(dev, dc->mat, (size_t)dc->nb_local_tiles * dc->bsiz * dc->elem_size);
+    const size_t elems = dc->lapack ? (size_t)dc->llm * dc->lln : (size_t)dc->nb_local_tiles * dc->bsiz;
+    return pb2_device_memory_register(dev, dc->mat, elems * dc->elem_size);
 }
 extern "C" int pb2_matrix_unregister_memory(pb2_matrix_block_cyclic_t* dc, pb2_device_t* dev) {
     if (!dc || !dev || !dc->mat) return PB2_ERR_BAD_PARAM;
@@ -188,6 +232,7 @@ __global__ void lcg_fill_tiles(T* out, const int2* tiles, int mb, int nb, int M,
 
 extern "C" int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev) {
     if (!dc || !dc->mat || !dev) return PB2_ERR_BAD_PARAM;
+    if (dc->lapack) return PB2_ERR_NOT_SUPPORTED;  // the generator writes packed tiles (the reference's does too)
     if (cudaSetDevice(pb2_device_cuda_index(dev)) != cudaSuccess) return PB2_ERR_DEVICE;
     // local tiles in storage order
     std::vector<int2> coords((size_t)dc->nb_local_tiles);
@@ -289,7 +334,7 @@ __global__ void lcg_fill_tiles_by_position(T* out, long long first_pos, int nb_e
 //     overlap on the same GPU (different host threads) would race on it -- serialise them.
 extern "C" int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev) {
     if (!dc || !dc->mat || !dev) return PB2_ERR_BAD_PARAM;
-    if (dc->i != 0 || dc->j != 0) return PB2_ERR_NOT_SUPPORTED;  // sub-matrix views: use pb2_matrix_fill_lcg
+    if (dc->i != 0 || dc->j != 0 || dc->lapack) return PB2_ERR_NOT_SUPPORTED;  // sub-matrix views: use pb2_matrix_fill_lcg
     const size_t tile_bytes = (size_t)dc->bsiz * dc->elem_size;
     if (tile_bytes > PB2_FILL_SCRATCH_BYTES) {
         fprintf(stderr,

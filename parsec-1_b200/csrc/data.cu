@@ -194,6 +194,27 @@ extern "C" pb2_data_t* pb2_data_create(uint64_t key, uint32_t dc_id, void* host_
     return d;
 }
 
+// A host tile that is a window of a larger column-major matrix (what stage_custom.jdf:28-109 handles with its own
+// stage functions and dc->llm): the default stage-in / stage-out and the write-back of evicted tiles then move
+// `height` columns of `width_bytes` with cudaMemcpy2DAsync, host pitch `host_pitch_bytes`, device pitch `dev_pitch_bytes`.
+extern "C" int pb2_data_set_host_layout(pb2_data_t* data, uint32_t width_bytes, uint32_t height, size_t host_pitch_bytes,
+                                        size_t dev_pitch_bytes) {
+    if (!data) return PB2_ERR_BAD_PARAM;
+    if (host_pitch_bytes == 0) {  // back to a packed tile
+        data->host_width = data->host_height = 0;
+        data->host_pitch = data->dev_pitch = 0;
+        return PB2_SUCCESS;
+    }
+    if (!width_bytes || !height || host_pitch_bytes < width_bytes || dev_pitch_bytes < width_bytes ||
+        (uint64_t)dev_pitch_bytes * height > data->nb_elts)
+        return PB2_ERR_BAD_PARAM;
+    data->host_width = width_bytes;
+    data->host_height = height;
+    data->host_pitch = host_pitch_bytes;
+    data->dev_pitch = dev_pitch_bytes;
+    return PB2_SUCCESS;
+}
+
 extern "C" int pb2_data_copy_version(const pb2_data_t* data, int dev, uint32_t* version) {
     if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return PB2_ERR_BAD_PARAM;
     const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];

@@ -340,21 +340,35 @@ extern "C" int64_t pb2_device_get_launch_ms(pb2_device_t* d, float* out, int64_t
 }
 
 // ------------------------------------------------------------------------------------ default staging
+// One tile between its host copy and a packed device tile.  A tile of a PARSEC_MATRIX_LAPACK collection is a window of
+// a column-major local matrix (pb2_data_set_host_layout): it goes through the copy engine's pitched 2D path, what the
+// reference leaves to user stage functions (stage_custom.jdf:28-109).
+static cudaError_t copy_tile(const pb2_data_s* data, void* dev, void* host, size_t bytes, bool to_device, cudaStream_t s) {
+    if (data && data->host_pitch) {
+        return to_device ? cudaMemcpy2DAsync(dev, data->dev_pitch, host, data->host_pitch, data->host_width,
+                                             data->host_height, cudaMemcpyHostToDevice, s)
+                         : cudaMemcpy2DAsync(host, data->host_pitch, dev, data->dev_pitch, data->host_width,
+                                             data->host_height, cudaMemcpyDeviceToHost, s);
+    }
+    return to_device ? cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, s)
+                     : cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s);
+}
+
 extern "C" int pb2_default_stage_in(pb2_gpu_task_t* t, uint32_t flow_mask, void* stream) {
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(flow_mask & (1u << i))) continue;
-        cudaError_t e = cudaMemcpyAsync(t->flow_dev_ptr[i], t->flow_host_ptr[i], t->flow_nb_elts[i],
-                                        cudaMemcpyHostToDevice, (cudaStream_t)stream);
-        if (e != cudaSuccess) return PB2_HOOK_RETURN_ERROR;
+        if (copy_tile(t->flow_data[i], t->flow_dev_ptr[i], t->flow_host_ptr[i], t->flow_nb_elts[i], true,
+                      (cudaStream_t)stream) != cudaSuccess)
+            return PB2_HOOK_RETURN_ERROR;
     }
     return PB2_SUCCESS;
 }
 extern "C" int pb2_default_stage_out(pb2_gpu_task_t* t, uint32_t flow_mask, void* stream) {
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(flow_mask & (1u << i))) continue;
-        cudaError_t e = cudaMemcpyAsync(t->flow_host_ptr[i], t->flow_dev_ptr[i], t->flow_nb_elts[i],
-                                        cudaMemcpyDeviceToHost, (cudaStream_t)stream);
-        if (e != cudaSuccess) return PB2_HOOK_RETURN_ERROR;
+        if (copy_tile(t->flow_data[i], t->flow_dev_ptr[i], t->flow_host_ptr[i], t->flow_nb_elts[i], false,
+                      (cudaStream_t)stream) != cudaSuccess)
+            return PB2_HOOK_RETURN_ERROR;
     }
     return PB2_SUCCESS;
 }
@@ -513,8 +527,7 @@ static bool start_w2r(pb2_device_s* d) {
     }
     // the dirty bytes were produced on exec streams whose completion the host has already observed
     for (pb2_copy_t* c : st->w2r_copies) {
-        cudaMemcpyAsync(c->original->host_copy.device_private, c->device_private, c->original->nb_elts,
-                        cudaMemcpyDeviceToHost, d->d2h);
+        copy_tile(c->original, c->device_private, c->original->host_copy.device_private, c->original->nb_elts, false, d->d2h);
         d->stats.data_out_to_host += c->original->nb_elts;
     }
     st->done = get_event(d);

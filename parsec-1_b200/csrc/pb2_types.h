@@ -45,6 +45,11 @@ struct pb2_data_s {
     int8_t owner_device = 0;
     int8_t preferred_device = -1;
     uint32_t nb_elts = 0;
+    // layout of the HOST tile when it is not packed (PARSEC_MATRIX_LAPACK storage: a window of a column-major local
+    // matrix): `host_height` runs of `host_width` bytes, `host_pitch` bytes apart; on the device the tile is packed with
+    // `dev_pitch` bytes per column.  host_pitch == 0: contiguous, nb_elts bytes (PARSEC_MATRIX_TILE).
+    uint32_t host_width = 0, host_height = 0;
+    size_t host_pitch = 0, dev_pitch = 0;
     pb2_copy_t host_copy;
     pb2_copy_t* device_copies[PB2_MAX_DEVICES] = {nullptr};
 };

@@ -101,6 +101,8 @@ def lib():
         "pb2_device_pop_workspace": (vp, [vp, vp, sz]), "pb2_device_push_workspace": (i32, [vp, vp]),
         "pb2_device_free_workspace": (i32, [vp]),
         "pb2_matrix_block_cyclic_new": (vp, [i32] * 16), "pb2_matrix_block_cyclic_free": (None, [vp]),
+        "pb2_matrix_block_cyclic_lapack_new": (vp, [i32] * 18), "pb2_matrix_tile_offset": (i64, [vp, i32, i32]),
+        "pb2_data_set_host_layout": (i32, [vp, u32, u32, sz, sz]),
         "pb2_matrix_set_mat": (i32, [vp, vp]), "pb2_matrix_nb_local_tiles": (i64, [vp]),
         "pb2_matrix_mt": (i32, [vp]), "pb2_matrix_nt": (i32, [vp]), "pb2_matrix_rank_of": (i32, [vp, i32, i32]),
         "pb2_matrix_position": (i64, [vp, i32, i32]), "pb2_matrix_data_key": (u64, [vp, i32, i32]),
@@ -169,14 +171,19 @@ class Device:
 class Matrix:
     """parsec_matrix_block_cyclic_t in tile storage, backed by a host buffer (numpy array or raw pointer)."""
 
-    def __init__(self, mtype, M, N, mb, nb, P=1, Q=1, rank=0, buf=None, kp=1, kq=1, ip=0, jq=0):
-        self.h = C.c_void_p(lib().pb2_matrix_block_cyclic_new(mtype, rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq))
+    def __init__(self, mtype, M, N, mb, nb, P=1, Q=1, rank=0, buf=None, kp=1, kq=1, ip=0, jq=0, lapack=None):
+        """lapack = (mloc, nloc): PARSEC_MATRIX_LAPACK storage, the buffer is a column-major mloc x nloc local matrix."""
+        if lapack:
+            self.h = C.c_void_p(lib().pb2_matrix_block_cyclic_lapack_new(mtype, rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq,
+                                                                         ip, jq, lapack[0], lapack[1]))
+        else:
+            self.h = C.c_void_p(lib().pb2_matrix_block_cyclic_new(mtype, rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq))
         if not self.h:
             raise ValueError("pb2_matrix_block_cyclic_new rejected the arguments")
         self.mtype, self.M, self.N, self.mb, self.nb = mtype, M, N, mb, nb
         self.elem = {MATRIX_DOUBLE: 8, MATRIX_FLOAT: 4, MATRIX_BF16: 2}[mtype]
         self.nb_local_tiles = lib().pb2_matrix_nb_local_tiles(self.h)
-        self.nbytes = self.nb_local_tiles * mb * nb * self.elem
+        self.nbytes = lapack[0] * lapack[1] * self.elem if lapack else self.nb_local_tiles * mb * nb * self.elem
         self.buf = None
         if buf is not None:
             self.set_buffer(buf)

@@ -184,9 +184,22 @@ def block_cyclic_cases():
             for (M, N, mb, nb) in [(1000, 1000, 96, 96), (640, 384, 64, 128)]
             for (P, Q, kp, kq, ip, jq) in [(1, 1, 2, 3, 0, 0), (2, 2, 2, 1, 0, 0), (2, 3, 2, 3, 0, 0), (3, 2, 3, 2, 1, 1),
                                            (2, 2, 1, 1, 1, 0)]]
-    for (M, N, mb, nb, P, Q, kp, kq, ip, jq) in plain + kcyc:
+    # PARSEC_MATRIX_LAPACK storage (parsec_matrix_block_cyclic_lapack_init): column-major local matrix, ld = mloc
+    ref.ref_bc_lapack_new.restype = C.c_void_p
+    ref.ref_bc_lapack_new.argtypes = [C.c_int] * 17
+    lapack = [(M, N, mb, nb, P, Q, kp, kq, ip, jq, True)
+              for (M, N, mb, nb) in [(1000, 1000, 96, 96), (250, 130, 40, 40)]
+              for (P, Q, kp, kq, ip, jq) in [(1, 1, 1, 1, 0, 0), (2, 2, 1, 1, 0, 0), (2, 3, 2, 1, 0, 0)]]
+    for spec in [c + (False,) for c in plain + kcyc] + lapack:
+            (M, N, mb, nb, P, Q, kp, kq, ip, jq, is_lapack) = spec
             for rank in range(P * Q):
                 dc = ref.ref_bc_new(rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq)
+                mloc = nloc = 0
+                if is_lapack:   # local matrix = the locally owned tile rows / columns, whole tiles (pad >= numroc)
+                    g0 = (C.c_int * 14)()
+                    ref.ref_bc_geometry(dc, g0)
+                    mloc, nloc = max(g0[9] * mb, 1), max(g0[10] * nb, 1)
+                    dc = ref.ref_bc_lapack_new(rank, mb, nb, M, N, 0, 0, M, N, P, Q, kp, kq, ip, jq, mloc, nloc)
                 g = (C.c_int * 14)()
                 ref.ref_bc_geometry(dc, g)
                 geo = dict(zip("mt nt lmt lnt lm ln llm lln bsiz nb_elem_r nb_elem_c nb_local_tiles rrank crank".split(), list(g)))
@@ -201,7 +214,7 @@ def block_cyclic_cases():
                             entry += [int(off), int(key.value), int(nbe.value)]
                         tiles.append(entry)
                 cases.append({"M": M, "N": N, "mb": mb, "nb": nb, "P": P, "Q": Q, "kp": kp, "kq": kq, "ip": ip, "jq": jq,
-                              "rank": rank, "geo": geo, "tiles": tiles})
+                              "lapack": [mloc, nloc] if is_lapack else None, "rank": rank, "geo": geo, "tiles": tiles})
     json.dump(cases, open(os.path.join(HERE, "block_cyclic.json"), "w"))
     print("wrote block_cyclic.json (%d descriptors, %d tiles)" % (len(cases), sum(len(c["tiles"]) for c in cases)))
 

@@ -11,7 +11,7 @@ _lib = None
 class BC(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
         "mb nb lm ln i j m n mt nt lmt lnt llm lln bsiz P Q kp kq ip jq rrank crank myrank "
-        "nb_elem_r nb_elem_c nb_local_tiles").split()]
+        "nb_elem_r nb_elem_c nb_local_tiles lapack").split()]
 
 
 class Counts(C.Structure):
@@ -41,6 +41,9 @@ def lib():
         L.orc_rnd64_jump.argtypes = [C.c_uint64, C.c_uint64]
         L.orc_init_tile.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_uint]
         L.orc_bc_init.argtypes = [C.POINTER(BC)] + [C.c_int] * 15
+        L.orc_bc_init_lapack.argtypes = [C.POINTER(BC)] + [C.c_int] * 17
+        L.orc_bc_offset.restype = C.c_int64
+        L.orc_bc_offset.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
         L.orc_bc_rank_of.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
         L.orc_bc_position.argtypes = [C.POINTER(BC), C.c_int, C.c_int]
         L.orc_bc_key.restype = C.c_uint64
@@ -74,6 +77,12 @@ def lib():
 def bc(myrank, mb, nb, lm, ln, i, j, m, n, P=1, Q=1, kp=1, kq=1, ip=0, jq=0):
     d = BC()
     lib().orc_bc_init(C.byref(d), myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq)
+    return d
+
+
+def bc_lapack(myrank, mb, nb, lm, ln, P, Q, kp, kq, ip, jq, mloc, nloc):
+    d = BC()
+    lib().orc_bc_init_lapack(C.byref(d), myrank, mb, nb, lm, ln, 0, 0, lm, ln, P, Q, kp, kq, ip, jq, mloc, nloc)
     return d
 
 
