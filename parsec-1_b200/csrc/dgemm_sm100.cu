@@ -334,6 +334,38 @@ dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ C
     // Epilogue.  acc[i][j][e]: row = m0 + 64wm + 8g + i, col = n0 + 32wn + 16(j>>1) + 4t + 2e + (j&1).
     const int row0 = m0 + wm * 64 + 8 * g;
     const bool rows_full = (row0 + 8 <= M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1);
+    if (rows_full && beta != 0.0) {
+        // C += A B (the task-graph case).  The old values of FOUR columns (16 x 16 bytes per thread) are requested
+        // before the first one is used: two L2 round trips per thread instead of eight -- a load cannot move above the
+        // store of the previous column on its own (same array), and 8 x ~0.7 us was ~4 % of a 1024^3 tile task.
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            double2 old[4][4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 2 * h + (c >> 1), e = c & 1;
+                const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+                const double2* cp = reinterpret_cast<const double2*>(C + (size_t)row0 + (size_t)min(col, N - 1) * ldc);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) old[c][q] = cp[q];  // a column past N re-reads column N-1 and is dropped below
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 2 * h + (c >> 1), e = c & 1;
+                const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+                if (col >= N) continue;
+                double2* cp = reinterpret_cast<double2*>(C + (size_t)row0 + (size_t)col * ldc);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    double2 v;
+                    v.x = alpha * acc[2 * q][j][e] + beta * old[c][q].x;
+                    v.y = alpha * acc[2 * q + 1][j][e] + beta * old[c][q].y;
+                    cp[q] = v;
+                }
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
 #pragma unroll
