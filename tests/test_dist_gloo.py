@@ -163,3 +163,44 @@ def test_two_gloo_ranks_reproduce_the_single_rank_result(tmp_path, P, Q, dist_sp
             assert np.array_equal(tile, want)  # same tile arithmetic in the same k order: bit-identical
             seen += 1
     assert seen == (N // NB) ** 2
+
+
+def test_plan_invariants_on_random_grids():
+    """Property test over random grids, k-cyclicities and origins: on every communicator all members issue the same
+    sequence with exactly one root per operation (the tile's owner), and every operand of every GEMM a rank owns is
+    local or received exactly once."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(1, 3), st.integers(1, 4), st.integers(1, 9), st.integers(1, 9), st.integers(1, 7), st.integers(1, 3),
+           st.integers(1, 3), st.integers(1, 3), st.integers(1, 3), st.integers(0, 2), st.integers(0, 3))
+    def check(P, Q, MT, NT, KT, kp, kq, a_kq, b_kp, ip, jq):
+        ip, jq = ip % P, jq % Q
+        spec = (kp, kq, a_kq, b_kp, ip, jq)
+        plans = {r: H.comm_plan(P, Q, r, MT, NT, KT, *spec) for r in range(P * Q)}
+        dA = O.bc(0, 1, 1, MT, KT, 0, 0, MT, KT, P, Q, kp, a_kq, ip, jq)
+        dB = O.bc(0, 1, 1, KT, NT, 0, 0, KT, NT, P, Q, b_kp, kq, ip, jq)
+        dC = O.bc(0, 1, 1, MT, NT, 0, 0, MT, NT, P, Q, kp, kq, ip, jq)
+        rank_of = lambda d, m, n: O.lib().orc_bc_rank_of(C.byref(d), m, n)
+        for which, members_of in ((0, lambda r: [(r // Q) * Q + c for c in range(Q)]),
+                                  (1, lambda r: [x * Q + (r % Q) for x in range(P)])):
+            for r in range(P * Q):
+                members = members_of(r)
+                seqs = [[op[:4] for op in plans[x] if op[0] == which] for x in members]
+                assert all(s == seqs[0] for s in seqs)
+                for i, (_, k, idx, root) in enumerate(seqs[0]):
+                    roots = [x for x in members if [op for op in plans[x] if op[0] == which][i][4]]
+                    owner = rank_of(dA, idx, k) if which == 0 else rank_of(dB, k, idx)
+                    assert roots == [owner] and members[root] == owner
+        for r, ops in plans.items():
+            keys = [(w, k, i) for (w, k, i, _, _) in ops]
+            assert len(keys) == len(set(keys))
+            got = set(keys)
+            for m in range(MT):
+                for n in range(NT):
+                    if rank_of(dC, m, n) == r:
+                        for k in range(KT):
+                            assert rank_of(dA, m, k) == r or (0, k, m) in got
+                            assert rank_of(dB, k, n) == r or (1, k, n) in got
+
+    check()
