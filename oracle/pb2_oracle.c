@@ -200,8 +200,10 @@ double orc_matrix_inf_norm_tiled(const orc_bc_t* dc, const double* mat) {
  * the reference does not vendor; this is the textbook definition C <- alpha*A*B + beta*C with the
  * k-sum taken in ascending order.
  * ====================================================================================== */
-void orc_dgemm_tile(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
-                    double beta, double* C, int ldc) {
+/* The definition, one column at a time.  Kept as the statement of what orc_dgemm_tile computes (and checked against it
+ * bit for bit in tests/test_oracle.py). */
+void orc_dgemm_tile_simple(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
+                           double beta, double* C, int ldc) {
     double* col = (double*)malloc(sizeof(double) * (size_t)(mb > 0 ? mb : 1));
     for (int j = 0; j < nb; ++j) {
         for (int i = 0; i < mb; ++i) col[i] = 0.0;
@@ -218,6 +220,66 @@ void orc_dgemm_tile(int mb, int nb, int kb, double alpha, const double* A, int l
             for (int i = 0; i < mb; ++i) cj[i] = alpha * col[i] + beta * cj[i];
     }
     free(col);
+}
+
+/* Same values, bit for bit (every element is still sum_k a_ik * b_kj taken in ascending k with a separate multiply and
+ * add, then alpha * sum + beta * c), arranged so that the host cores are not waiting on memory: 8 rows of A are packed
+ * into a k-major panel once and swept against 4 columns of B with the 8 x 4 sums held in registers.  About 4x the
+ * one-column-at-a-time form; still plain C without fused multiply-add, not a tuned BLAS. */
+#include <immintrin.h>
+void orc_dgemm_tile(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
+                    double beta, double* C, int ldc) {
+    if (mb <= 0 || nb <= 0) return;
+    double* Ap = (double*)aligned_alloc(64, sizeof(double) * 8 * (size_t)(kb > 0 ? kb : 1));
+    for (int i0 = 0; i0 < mb; i0 += 8) {
+        const int ib = mb - i0 < 8 ? mb - i0 : 8;
+        for (int k = 0; k < kb; ++k)
+            for (int r = 0; r < 8; ++r) Ap[(size_t)k * 8 + r] = r < ib ? A[(size_t)k * lda + i0 + r] : 0.0;
+        for (int j0 = 0; j0 < nb; j0 += 4) {
+            const int jb = nb - j0 < 4 ? nb - j0 : 4;
+            double sum[4][8];
+            if (jb == 4) {
+                __m256d c00 = _mm256_setzero_pd(), c01 = c00, c10 = c00, c11 = c00, c20 = c00, c21 = c00, c30 = c00, c31 = c00;
+                const double *b0 = B + (size_t)j0 * ldb, *b1 = b0 + ldb, *b2 = b1 + ldb, *b3 = b2 + ldb;
+                for (int k = 0; k < kb; ++k) {
+                    const __m256d a0 = _mm256_load_pd(Ap + (size_t)k * 8), a1 = _mm256_load_pd(Ap + (size_t)k * 8 + 4);
+                    __m256d b = _mm256_broadcast_sd(b0 + k);
+                    c00 = _mm256_add_pd(c00, _mm256_mul_pd(a0, b));
+                    c01 = _mm256_add_pd(c01, _mm256_mul_pd(a1, b));
+                    b = _mm256_broadcast_sd(b1 + k);
+                    c10 = _mm256_add_pd(c10, _mm256_mul_pd(a0, b));
+                    c11 = _mm256_add_pd(c11, _mm256_mul_pd(a1, b));
+                    b = _mm256_broadcast_sd(b2 + k);
+                    c20 = _mm256_add_pd(c20, _mm256_mul_pd(a0, b));
+                    c21 = _mm256_add_pd(c21, _mm256_mul_pd(a1, b));
+                    b = _mm256_broadcast_sd(b3 + k);
+                    c30 = _mm256_add_pd(c30, _mm256_mul_pd(a0, b));
+                    c31 = _mm256_add_pd(c31, _mm256_mul_pd(a1, b));
+                }
+                _mm256_storeu_pd(sum[0], c00); _mm256_storeu_pd(sum[0] + 4, c01);
+                _mm256_storeu_pd(sum[1], c10); _mm256_storeu_pd(sum[1] + 4, c11);
+                _mm256_storeu_pd(sum[2], c20); _mm256_storeu_pd(sum[2] + 4, c21);
+                _mm256_storeu_pd(sum[3], c30); _mm256_storeu_pd(sum[3] + 4, c31);
+            } else {
+                for (int jj = 0; jj < jb; ++jj) {
+                    for (int r = 0; r < 8; ++r) sum[jj][r] = 0.0;
+                    const double* bj = B + (size_t)(j0 + jj) * ldb;
+                    for (int k = 0; k < kb; ++k) {
+                        const double bkj = bj[k];
+                        for (int r = 0; r < 8; ++r) sum[jj][r] += Ap[(size_t)k * 8 + r] * bkj;
+                    }
+                }
+            }
+            for (int jj = 0; jj < jb; ++jj) {
+                double* cj = C + (size_t)(j0 + jj) * ldc + i0;
+                if (beta == 0.0)
+                    for (int r = 0; r < ib; ++r) cj[r] = alpha * sum[jj][r];
+                else
+                    for (int r = 0; r < ib; ++r) cj[r] = alpha * sum[jj][r] + beta * cj[r];
+            }
+        }
+    }
+    free(Ap);
 }
 
 uint16_t orc_f32_to_bf16_rn(float x) {

@@ -63,6 +63,9 @@ void orc_bc_fill(const orc_bc_t* dc, double* mat, unsigned seed, int nthreads);
 /* ---- tile GEMM and the tiled GEMM DAG --------------------------------------------------- */
 void orc_dgemm_tile(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
                     double beta, double* C, int ldc);
+/* the same values from the one-column-at-a-time form of the definition (the two are compared bit for bit) */
+void orc_dgemm_tile_simple(int mb, int nb, int kb, double alpha, const double* A, int lda, const double* B, int ldb,
+                           double beta, double* C, int ldc);
 
 typedef struct orc_counts_s {
     int64_t gemm, read_a, read_b;

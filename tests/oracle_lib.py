@@ -53,6 +53,7 @@ def lib():
         L.orc_bc_fill.argtypes = [C.POINTER(BC), C.c_void_p, C.c_uint, C.c_int]
         L.orc_dgemm_tile.argtypes = [C.c_int] * 3 + [C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                                      C.c_double, C.c_void_p, C.c_int]
+        L.orc_dgemm_tile_simple.argtypes = L.orc_dgemm_tile.argtypes
         L.orc_tiled_dgemm.argtypes = [C.c_int] * 6 + [C.c_void_p] * 3 + [C.c_int, C.POINTER(Counts), C.c_void_p]
         L.orc_gemm_tile_bf16.argtypes = [C.c_int] * 3 + [C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                                          C.c_float, C.c_void_p, C.c_int]

@@ -164,6 +164,24 @@ def test_dgemm_tile_vs_numpy():
         assert np.allclose(Cm, want, rtol=0, atol=1e-12 * kb)
 
 
+@pytest.mark.parametrize("m,n,k,alpha,beta", [(256, 256, 256, 1.0, 1.0), (100, 37, 53, -1.5, 0.5), (8, 4, 1, 1.0, 0.0),
+                                              (7, 3, 9, 2.0, 1.0), (129, 130, 131, 1.0, 0.0), (1, 1, 1, 1.0, 1.0),
+                                              (16, 8, 0, 1.0, 0.5), (64, 1, 64, 1.0, 1.0), (5, 64, 64, 0.0, 2.0)])
+def test_register_blocked_tile_gemm_is_the_definition_bit_for_bit(m, n, k, alpha, beta):
+    """orc_dgemm_tile packs 8 rows of A and keeps 8 x 4 sums in registers; every element is still the ascending-k sum with
+    a separate multiply and add, so it must reproduce the one-column-at-a-time statement of the definition exactly."""
+    rng = np.random.default_rng(m * 131 + n * 17 + k)
+    kk = max(k, 1)
+    a = np.asfortranarray(rng.uniform(-0.5, 0.5, (m, kk)))
+    b = np.asfortranarray(rng.uniform(-0.5, 0.5, (kk, n)))
+    c1 = np.asfortranarray(rng.uniform(-0.5, 0.5, (m, n)))
+    c2 = c1.copy(order="F")
+    L = O.lib()
+    L.orc_dgemm_tile(m, n, k, alpha, a.ctypes.data, m, b.ctypes.data, kk, beta, c1.ctypes.data, m)
+    L.orc_dgemm_tile_simple(m, n, k, alpha, a.ctypes.data, m, b.ctypes.data, kk, beta, c2.ctypes.data, m)
+    assert np.array_equal(c1, c2)
+
+
 def test_tiled_dgemm_config1_counts_versions_and_values():
     """BASELINE config 1: N=2048, NB=256 -> 512 GEMM + 64 READ_A + 64 READ_B tasks, C versions == KT == 8
     (the values the reference runtime produced in the survey probe)."""
