@@ -139,8 +139,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=32768, help="matrix order (BASELINE configs[1]: 32768)")
     ap.add_argument("--nb", type=int, default=1024, help="tile size")
-    ap.add_argument("--cpu-n", type=int, default=12288,
-                    help="matrix order of the bounded CPU sample (12288: about 15 s of CPU work on 16 cores)")
+    ap.add_argument("--cpu-n", type=int, default=16384,
+                    help="matrix order of the bounded CPU sample (16384: about 15 s of CPU work on the GPU box's 16 cores)")
     ap.add_argument("--window", type=int, default=0, help="C-tile chains in flight (0 = the taskpool default: 128, or 16 for tensor-core bodies)")
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=18, help="h2d + d2h + exec streams (the module spreads a task over as "
