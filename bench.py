@@ -320,7 +320,7 @@ def main():
                      "kernel": "pb2::gemm_umma_pair" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
                      "detail": prof, "algorithmic_flops_per_launch": per_launch_flops},
     }
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:   # the CPU baseline is a single-GPU-run figure (N = 1 only)
         threads = os.cpu_count() or 1
         g, dt = cpu_port_gflops(args.cpu_n, NB, threads)
         out["cpu_baseline"] = {"value": g, "unit": "GFLOP/s", "cores": threads, "kind": "port",
