@@ -316,7 +316,7 @@ def main():
         "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": (achieved_tf / peak_tf) if prof else None,
                      # dram bytes per launch from one ncu --set full capture (profiles/dgemm_tma_r1_ncu.md)
-                     "traffic": None if bf16 else 25206528,
+                     "traffic": 25206528 if (not bf16 and NB == 1024) else None,
                      "kernel": "pb2::gemm_umma_pair" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
                      "detail": prof, "algorithmic_flops_per_launch": per_launch_flops},
     }
