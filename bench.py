@@ -149,6 +149,9 @@ def main():
     ap.add_argument("--hbm-gib", type=float, default=0.0,
                     help="cap the HBM tile heap (GiB) to run out of core: the BASELINE configs[3] mechanism (LRU evict + "
                          "write-back) at a size the box's host memory allows; 0 = 95%% of free HBM")
+    ap.add_argument("--strong", action="store_true",
+                    help="N>1: keep --n fixed as GPUs are added (BASELINE configs[2] as written: --n 65536 on 2/4/8 GPUs) "
+                         "instead of the default weak scaling N_g = n * g^(1/3)")
     ap.add_argument("--replicas", action="store_true",
                     help="diagnostic for N>1: independent 1x1 problems per GPU (isolates box effects from the data plane)")
     ap.add_argument("--dtype", default="f64", choices=["f64", "bf16"],
@@ -178,7 +181,7 @@ def main():
 
     NB = args.nb
     # weak scaling: flops per GPU constant, N_g = N_1 * g^(1/3) rounded to a whole number of tiles
-    N = args.n if world == 1 else int(round(args.n * world ** (1.0 / 3.0) / NB)) * NB
+    N = args.n if (world == 1 or args.strong) else int(round(args.n * world ** (1.0 / 3.0) / NB)) * NB
     P, Q = H.grid_for(world)
     if args.replicas:   # diagnostic: every rank runs its own 1x1 problem, no data-plane traffic at all
         N, P, Q = args.n, 1, 1
@@ -287,14 +290,17 @@ def main():
     tile_bytes = NB * NB * 8
     out = {
         "metric": "tiled GEMM GFLOP/s", "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(3, args.warmup), "ms_per_step": ms_resident, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(3, args.warmup), "ms_per_step": ms_resident, "higher_is_better": True,
+        "scaling": "strong" if (args.strong and world > 1) else "weak",
         "vs_baseline": None, "dtype": "bf16 in / f32 accumulate" if bf16 else "f64", "data": "synthetic",
         "config": {"workload": ("mixed-precision tiled GEMM BF16-in/FP32-acc N=%d NB=%d via tcgen05 on %d B200 "
                                 "(BASELINE configs[4] shape)" % (N, NB, world)) if bf16 else
                                ("tiled DGEMM N=%d NB=%d fp64 on 1 B200 via CUDA BODY + device stage-in/out "
                                 "(BASELINE configs[1])" % (N, NB)) if world == 1 else
                                ("tiled DGEMM N=%d NB=%d fp64, 2D block-cyclic %dx%d over %d B200 with NCCL tile bcast "
-                                "(BASELINE configs[2] shape; weak scaling from N=%d)" % (N, NB, P, Q, world, args.n)),
+                                "(BASELINE configs[2] shape; %s)" % (N, NB, P, Q, world,
+                                                                    "strong scaling, N fixed" if args.strong else
+                                                                    "weak scaling from N=%d" % args.n)),
                    "tasks_per_step": (N // NB) ** 3, "host_cores": os.cpu_count(), "replicas_diagnostic": bool(args.replicas),
                    "l2": "inputs (%.1f GiB) far larger than L2" % (N * N * (8 if bf16 else 24) / 2 ** 30),
                    "parallelism": "1 process per GPU, %dx%d grid; %s exec streams in use per GPU" % (
