@@ -81,12 +81,15 @@ int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, f
 int parsec_b200_gemm_tf32_sm100(char transa, char transb, int m, int n, int k, float alpha, const float* A, int lda,
                                 const float* B, int ldb, float beta, float* C, int ldc, void* stream);
 
-/* HBM heap: zone_malloc_init / zone_malloc / zone_free / zone_in_use (parsec/utils/zone_malloc.h:41-63).  The device
- * module owns one per GPU; these handles let a test compare placement decisions with the reference allocator
- * offset by offset, without a GPU (the base address is symbolic). */
+/* HBM heap: the job of zone_malloc_init / zone_malloc / zone_free / zone_in_use (parsec/utils/zone_malloc.h:41-63) --
+ * carve the module's one device allocation into tiles, in units of `unit_size` bytes -- with a policy of its own: a
+ * freed extent waits on a stack of extents of its size and is handed to the next request of that size (O(1) both
+ * ways: a tile cache asks for one or two sizes); other requests are carved from the lowest run of the coalesced
+ * free space, into which the stacks are merged when a request cannot be served otherwise.  The device module owns
+ * one per GPU; these handles let a test drive the heap without a GPU (the base address is symbolic). */
 void* pb2_zone_create(int max_segment, size_t unit_size);
 void pb2_zone_destroy(void* zone);
-int64_t pb2_zone_malloc(void* zone, size_t size); /* byte offset from the base, -1 = no segment fits */
+int64_t pb2_zone_malloc(void* zone, size_t size); /* byte offset from the base, -1 = no run of free units is long enough */
 int pb2_zone_free(void* zone, int64_t offset);
 size_t pb2_zone_in_use(void* zone);
 
@@ -114,6 +117,25 @@ int pb2_data_copy_readers(const pb2_data_t* data, int device_index);
 int pb2_data_owner_device(const pb2_data_t* data);
 void* pb2_data_copy_ptr(const pb2_data_t* data, int device_index); /* PARSEC_DATA_COPY_GET_PTR */
 
+/* Overlay support (overlay/device_cuda_b200_shim.c, the file compiled in place of
+ * parsec/mca/device/cuda/device_cuda_module.c): a parsec_data_t keeps a pb2 mirror.  `user` is the shim's
+ * parsec_data_copy_t of the device; pb2_data_sync_host copies what the runtime's host copy says (address, version,
+ * coherency or -1 = keep) into the mirror before a task is submitted, where the reference's stage-in reads
+ * task->data[i].data_in directly (device_cuda_module.c:1260-1300); pb2_data_get_state reads the device side back so the
+ * shim can write it into the real parsec_data_copy_t (version, coherency_state, readers, device_private) and
+ * parsec_data_t.owner_device. */
+void pb2_data_set_user(pb2_data_t* data, void* user);
+void* pb2_data_user(const pb2_data_t* data);
+int pb2_data_sync_host(pb2_data_t* data, void* host_ptr, uint32_t version, int coherency);
+typedef struct pb2_data_state_s {
+    void* dev_ptr;
+    uint32_t dev_version, host_version;
+    int32_t readers;
+    uint8_t dev_coherency, host_coherency, has_copy;
+    int8_t owner_device; /* pb2 device index, 0 = host, -1 = none */
+} pb2_data_state_t;
+int pb2_data_get_state(const pb2_data_t* data, int device_index, pb2_data_state_t* out);
+
 /* The ownership / coherency state machine on bare copies (no device needed): parsec_data_copy_attach / _detach and
  * parsec_data_start / end_transfer_ownership_to_copy (parsec/data.c:163-202, :299-433).  A CPU test replays operation
  * sequences recorded from the reference's own data.c through these (tests/golden/ownership_trace.json). */
@@ -138,8 +160,20 @@ typedef struct pb2_device_params_s {
     int profile_launches;         /* time every body launch with CUDA events on its exec stream (bench.py roofline) */
     int sort_pending_tasks;       /* device_cuda_sort_pending_tasks (0): among the first 10 pending tasks take the one
                                      that needs the fewest new tiles (parsec_gpu_sort_pending_list, device_gpu.c:117-166) */
+    int prefetch_deferred;        /* 1: a PREFETCH advice given while nobody manages the device is only queued, like the
+                                     reference's push to `pending` (device_cuda_module.c:1668); the next manager runs it.
+                                     0 (default): the adviser drives the device until the prefetch is done */
 } pb2_device_params_t;
 void pb2_device_params_default(pb2_device_params_t* p);
+/* The reference's MCA parameter names, as they reach a process in its environment (PARSEC_MCA_<name>,
+ * parsec/utils/mca_param.c): device_cuda_memory_use, _memory_block_size, _memory_number_of_blocks, _max_streams,
+ * _max_number_of_ejected_data, _sort_pending_tasks (device_cuda_component.c:163-206) overwrite the matching fields;
+ * returns how many were found.  pb2_device_create(idx, NULL, ..) applies the defaults, then these.  Inside a PaRSEC
+ * build the overlay shim passes the values the runtime itself parsed (files, environment, --mca on the command line). */
+int pb2_device_params_from_env(pb2_device_params_t* p);
+/* device_cuda_enabled (-1 = all GPUs, n = the first n, 0 = none) and device_cuda_mask (bit i), same source:
+ * 1 when GPU `cuda_index` may be used.  pb2_device_create(idx, NULL, ..) refuses a disabled GPU (PB2_ERR_NOT_SUPPORTED). */
+int pb2_device_is_enabled(int cuda_index);
 
 /* parsec_cuda_module_init (device_cuda_module.c:325-547): streams, events, one cudaMalloc carved by the zone
  * allocator.  The device gets index 2 + (number of devices created before it), as in parsec_mca_device_add. */
@@ -156,6 +190,22 @@ int pb2_device_memory_release(pb2_device_t* dev);
 /* parsec_cuda_data_advise (:1611-1679) */
 int pb2_device_data_advise(pb2_device_t* dev, pb2_data_t* data, int advice);
 
+/* Overlay support.  copy_released: the module has just given back the HBM of `data`'s device copy (LRU eviction,
+ * memory_release, destroy) -- where the reference detaches and releases the parsec_data_copy_t
+ * (device_cuda_module.c:1090-1110); called on the manager thread.  data_alive: asked before a dirty tile is written
+ * back to its host copy; 0 = the runtime has destroyed the data, the tile is dropped instead. */
+typedef struct pb2_device_hooks_s {
+    void (*copy_released)(pb2_device_t* dev, pb2_data_t* data, void* user);
+    int (*data_alive)(pb2_device_t* dev, pb2_data_t* data, void* user);
+} pb2_device_hooks_t;
+int pb2_device_set_hooks(pb2_device_t* dev, const pb2_device_hooks_t* hooks);
+/* The module's CUDA streams, numbered like parsec_device_gpu_module_t.exec_stream[] (device_cuda_module.c:414-420):
+ * 0 = h2d, 1 = d2h, 2.. = exec.  pb2_device_stream_index maps the cuda_stream a submit / stage callback received
+ * back to that number (-1 = not one of ours). */
+int pb2_device_nb_streams(const pb2_device_t* dev);
+void* pb2_device_stream(const pb2_device_t* dev, int index);
+int pb2_device_stream_index(const pb2_device_t* dev, const void* cuda_stream);
+
 /* statistics of parsec_device_module_t (parsec/mca/device/device.h:132-137) plus cache counters */
 typedef struct pb2_device_stats_s {
     uint64_t executed_tasks, data_in_from_host, data_in_from_peers, data_out_to_host;
@@ -165,6 +215,9 @@ typedef struct pb2_device_stats_s {
     uint64_t host_submit_ns, host_retire_ns; /* manager-thread time spent submitting / retiring tasks */
 } pb2_device_stats_t;
 int pb2_device_get_stats(pb2_device_t* dev, pb2_device_stats_t* out, int reset);
+/* the live counters, for a caller on the manager thread that folds them into its own after every task (the overlay
+ * shim does, into parsec_device_module_t); hbm_bytes_in_use is only refreshed by pb2_device_get_stats */
+const pb2_device_stats_t* pb2_device_stats_live(const pb2_device_t* dev);
 
 /* Data-state trace (enabled by params.trace_events); same layout as the oracle's orc_event_t. */
 typedef struct pb2_event_s {
@@ -290,7 +343,9 @@ int pb2_matrix_fill_lcg(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device
  * pb2_device_create has handed 95 % of HBM to the tile heap (a staging cudaMalloc may then fail), or while the
  * pipeline is busy (cudaMalloc / cudaFree synchronise the device).  Has no counterpart in the reference.
  * Tiles are staged through a 16 MiB buffer that is part of the library image on every GPU that loads it, so one tile
- * may be at most 16 MiB; larger tiles return PB2_ERR_VALUE_OUT_OF_BOUNDS (-8).  The first call on a device resolves
+ * may be at most 16 MiB; larger tiles return PB2_ERR_VALUE_OUT_OF_BOUNDS (-8).  Plain, k-cyclic and origin-shifted
+ * grids are handled; a sub-matrix view (i, j != 0, or fewer tiles than the parent stores) and LAPACK storage return
+ * PB2_ERR_NOT_SUPPORTED (-7) and leave the matrix untouched.  The first call on a device resolves
  * the buffer's address and should come before any stream capture.  All calls on a device share that buffer (it keeps
  * the previous call's bytes; nothing needs it zeroed), so calls that overlap on one GPU race: serialise them. */
 int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev);

@@ -306,14 +306,18 @@ static int fill_scratch_address(int cuda_index, void** out) {
 
 // Same arithmetic as lcg_fill_tiles; the tile coordinates are derived from the storage position instead of being read
 // from a coordinate table (which would be one more buffer to allocate).
+// pb2_matrix_position inverted: a rank stores its tiles column by column, nb_elem_r per local column; with k-cyclic
+// super-tiles local row l is global row (l / kp) * kp * P + rrank * kp + l % kp (two_dim_rectangle_cyclic.c:652-664
+// read backwards), and the same for columns with kq, Q, crank.  kp = kq = 1 gives l * P + rrank.
 template <typename T>
-__global__ void lcg_fill_tiles_by_position(T* out, long long first_pos, int nb_elem_r, int P, int Q, int rrank, int crank,
-                                           int mb, int nb, int M, unsigned seed) {
+__global__ void lcg_fill_tiles_by_position(T* out, long long first_pos, int nb_elem_r, int P, int Q, int kp, int kq,
+                                           int rrank, int crank, int mb, int nb, int M, unsigned seed) {
     const int col = blockIdx.x * blockDim.x + threadIdx.x;
     if (col >= nb) return;
     const long long pos = first_pos + blockIdx.y;
-    const int m = (int)(pos % nb_elem_r) * P + rrank;
-    const int n = (int)(pos / nb_elem_r) * Q + crank;
+    const int lrow = (int)(pos % nb_elem_r), lcol = (int)(pos / nb_elem_r);
+    const int m = (lrow / kp) * kp * P + rrank * kp + lrow % kp;
+    const int n = (lcol / kq) * kq * Q + crank * kq + lcol % kq;
     unsigned long long jump = (unsigned long long)m + ((unsigned long long)n + (unsigned long long)col) * (unsigned long long)M;
     unsigned long long x = lcg_jump(jump, seed);
     T* p = out + (size_t)blockIdx.y * mb * nb + (size_t)col * mb;
@@ -334,7 +338,8 @@ __global__ void lcg_fill_tiles_by_position(T* out, long long first_pos, int nb_e
 //     overlap on the same GPU (different host threads) would race on it -- serialise them.
 extern "C" int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsigned seed, pb2_device_t* dev) {
     if (!dc || !dc->mat || !dev) return PB2_ERR_BAD_PARAM;
-    if (dc->i != 0 || dc->j != 0 || dc->lapack) return PB2_ERR_NOT_SUPPORTED;  // sub-matrix views: use pb2_matrix_fill_lcg
+    // sub-matrix views (an origin, or fewer tiles than the parent matrix stores) and LAPACK storage: pb2_matrix_fill_lcg
+    if (dc->i != 0 || dc->j != 0 || dc->mt != dc->lmt || dc->nt != dc->lnt || dc->lapack) return PB2_ERR_NOT_SUPPORTED;
     const size_t tile_bytes = (size_t)dc->bsiz * dc->elem_size;
     if (tile_bytes > PB2_FILL_SCRATCH_BYTES) {
         fprintf(stderr,
@@ -353,14 +358,14 @@ extern "C" int pb2_matrix_fill_lcg_noalloc(pb2_matrix_block_cyclic_t* dc, unsign
         const int nt = (int)std::min<long long>(batch, dc->nb_local_tiles - t0);
         dim3 grid((dc->nb + 127) / 128, nt);
         if (dc->mtype == PB2_MATRIX_DOUBLE)
-            lcg_fill_tiles_by_position<double><<<grid, 128>>>((double*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->rrank,
-                                                              dc->crank, dc->mb, dc->nb, dc->m, seed);
+            lcg_fill_tiles_by_position<double><<<grid, 128>>>((double*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->kp, dc->kq,
+                                                              dc->rrank, dc->crank, dc->mb, dc->nb, dc->m, seed);
         else if (dc->mtype == PB2_MATRIX_FLOAT)
-            lcg_fill_tiles_by_position<float><<<grid, 128>>>((float*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->rrank,
-                                                             dc->crank, dc->mb, dc->nb, dc->m, seed);
+            lcg_fill_tiles_by_position<float><<<grid, 128>>>((float*)scratch, t0, dc->nb_elem_r, dc->P, dc->Q, dc->kp, dc->kq,
+                                                             dc->rrank, dc->crank, dc->mb, dc->nb, dc->m, seed);
         else
             lcg_fill_tiles_by_position<__nv_bfloat16><<<grid, 128>>>((__nv_bfloat16*)scratch, t0, dc->nb_elem_r, dc->P,
-                                                                     dc->Q, dc->rrank, dc->crank, dc->mb, dc->nb, dc->m,
+                                                                     dc->Q, dc->kp, dc->kq, dc->rrank, dc->crank, dc->mb, dc->nb, dc->m,
                                                                      seed);
         if (cudaGetLastError() != cudaSuccess) return PB2_ERR_DEVICE;
         if (cudaMemcpy((char*)dc->mat + (size_t)t0 * tile_bytes, scratch, tile_bytes * nt, cudaMemcpyDeviceToHost) !=

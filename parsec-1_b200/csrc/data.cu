@@ -2,10 +2,12 @@
 // LRU lists.  Host-only code (compiled by nvcc with the rest of the library).
 //
 // Behavioural contract kept from the reference (the generated code and the graded version sequences
-// depend on it):  parsec/data.c:484-522 (create), :319-433 (start of an ownership transfer),
-// :299-317 (end), parsec/utils/zone_malloc.c (first fit + coalescing).
+// depend on it):  parsec/data.c:484-522 (create), :319-433 (start of an ownership transfer), :299-317 (end).
+// The heap only shares its job with parsec/utils/zone_malloc.c (carve one device allocation); its policy is its own.
 #include <stdlib.h>
 #include <string.h>
+
+#include <iterator>
 
 #include "pb2_internal.h"
 #include "pb2_types.h"
@@ -65,78 +67,74 @@ void data_end_transfer_ownership(pb2_data_s* data, int device, uint8_t access) {
 }
 
 // ------------------------------------------------------------------------------------------ heap
-ZoneHeap::ZoneHeap(char* base, int max_segment, size_t unit)
-    : base_(base), seg_((size_t)max_segment), nseg_(max_segment), cursor_(0), unit_(unit) {
-    memset(seg_.data(), 0, sizeof(Seg) * seg_.size());
-    seg_[0].busy = 0;
-    seg_[0].units = max_segment;
-    seg_[0].before = 1;
+ZoneHeap::ZoneHeap(char* base, int nb_units, size_t unit)
+    : base_(base), nunits_((uint32_t)(nb_units > 0 ? nb_units : 0)), unit_(unit), len_at_((size_t)nunits_, 0u) {
+    if (nunits_) runs_[0] = nunits_;
+}
+
+// lowest-addressed run that is long enough; the remainder stays a run
+bool ZoneHeap::carve(uint32_t want, uint32_t* at) {
+    for (auto it = runs_.begin(); it != runs_.end(); ++it) {
+        if (it->second < want) continue;
+        const uint32_t start = it->first, len = it->second;
+        runs_.erase(it);
+        if (len > want) runs_[start + want] = len - want;
+        *at = start;
+        return true;
+    }
+    return false;
+}
+
+// put a free extent into the map, merging it with the runs that touch it
+void ZoneHeap::merge_in(uint32_t at, uint32_t len) {
+    auto next = runs_.lower_bound(at);
+    if (next != runs_.begin()) {
+        auto prev = std::prev(next);
+        if (prev->first + prev->second == at) {
+            at = prev->first;
+            len += prev->second;
+            runs_.erase(prev);
+        }
+    }
+    if (next != runs_.end() && at + len == next->first) {
+        len += next->second;
+        runs_.erase(next);
+    }
+    runs_[at] = len;
 }
 
 void* ZoneHeap::alloc(size_t size) {
-    const int want = (int)((size + unit_ - 1) / unit_);
-    int id = cursor_;
-    bool wrapped = false;
-    do {
-        Seg* s = at(id);
-        if (!s) {
-            if (wrapped) return nullptr;
-            wrapped = true;
-            id = 0;
-            s = at(0);
+    if (size == 0 || size > capacity()) return nullptr;
+    const uint32_t want = (uint32_t)((size + unit_ - 1) / unit_);
+    uint32_t at = 0;
+    auto parked = parked_.find(want);
+    if (parked != parked_.end() && !parked->second.empty()) {
+        at = parked->second.back();
+        parked->second.pop_back();
+    } else if (!carve(want, &at)) {
+        bool any = false;
+        for (auto& kv : parked_) {
+            for (uint32_t off : kv.second) merge_in(off, kv.first);
+            any = any || !kv.second.empty();
+            kv.second.clear();
         }
-        if (!s->busy && s->units >= want) {
-            s->busy = 1;
-            if (s->units > want) {
-                if (Seg* after = at(id + s->units)) after->before -= want;
-                Seg* rest = at(id + want);
-                rest->busy = 0;
-                rest->before = want;
-                rest->units = s->units - want;
-                cursor_ = id + want;
-                s->units = want;
-            }
-            return base_ + (size_t)id * unit_;
-        }
-        id += s->units;
-    } while (id != cursor_);
-    return nullptr;
+        if (!any || !carve(want, &at)) return nullptr;
+    }
+    len_at_[at] = want;
+    used_units_ += want;
+    return base_ + (size_t)at * unit_;
 }
 
 bool ZoneHeap::free(void* p) {
-    int64_t off = (char*)p - base_;
-    if (off < 0 || off % (int64_t)unit_) return false;
-    int id = (int)(off / (int64_t)unit_);
-    Seg* s = at(id);
-    if (!s || !s->busy) return false;
-    s->busy = 0;
-    int pid = id - s->before, nid = id + s->units;
-    Seg* prev = at(pid);
-    Seg* next = at(nid);
-    if (prev && !prev->busy) {
-        if (next) next->before += prev->units;
-        prev->units += s->units;
-        s = prev;
-        id = pid;
-    }
-    cursor_ = id;
-    if (next && !next->busy) {
-        nid += next->units;
-        s->units += next->units;
-        next = at(nid);
-        if (next) next->before = s->units;
-    }
+    const int64_t off = (char*)p - base_;
+    if (off < 0 || off % (int64_t)unit_ || (uint64_t)off / unit_ >= nunits_) return false;
+    const uint32_t at = (uint32_t)((uint64_t)off / unit_);
+    const uint32_t len = len_at_[at];
+    if (!len) return false;  // not the start of a live extent (double free included)
+    len_at_[at] = 0;
+    used_units_ -= len;
+    parked_[len].push_back(at);
     return true;
-}
-
-size_t ZoneHeap::in_use() const {
-    size_t used = 0;
-    for (int id = 0; id < nseg_;) {
-        const Seg& s = seg_[id];
-        if (s.busy) used += unit_ * (size_t)s.units;
-        id += s.units;
-    }
-    return used;
 }
 
 // ------------------------------------------------------------------------------------------ lists
@@ -237,6 +235,49 @@ extern "C" void* pb2_data_copy_ptr(const pb2_data_t* data, int dev) {
     if (!data || dev < 0 || dev >= PB2_MAX_DEVICES) return nullptr;
     const pb2_copy_t* c = dev == 0 ? &data->host_copy : data->device_copies[dev];
     return c ? c->device_private : nullptr;
+}
+
+// ------------------------------------------------------------------------------------------ overlay support
+// What the shim that stands in for device_cuda_module.c inside a PaRSEC build (overlay/device_cuda_b200_shim.c) needs
+// to keep a parsec_data_t and its pb2 mirror in step.
+extern "C" void pb2_data_set_user(pb2_data_t* data, void* user) {
+    if (data) data->user = user;
+}
+extern "C" void* pb2_data_user(const pb2_data_t* data) { return data ? data->user : nullptr; }
+
+// The host side of a tile is owned by the runtime: before a task is handed to the module the shim copies what the
+// runtime's host copy says (address, version, and OWNED when a CPU task wrote it since) into the mirror.
+extern "C" int pb2_data_sync_host(pb2_data_t* data, void* host_ptr, uint32_t version, int coherency) {
+    if (!data) return PB2_ERR_BAD_PARAM;
+    std::lock_guard<std::mutex> g(data->lock);
+    data->host_copy.device_private = host_ptr;
+    data->host_copy.version = version;
+    if (coherency >= 0 && coherency != data->host_copy.coherency_state) {
+        data->host_copy.coherency_state = (uint8_t)coherency;
+        if (coherency == PB2_DATA_COHERENCY_OWNED) {
+            // a CPU writer took the tile: every device copy that is not in use falls back to SHARED (data.c:398-404)
+            data->owner_device = 0;
+            for (int d = 1; d < PB2_MAX_DEVICES; ++d)
+                if (data->device_copies[d] && data->device_copies[d]->coherency_state == PB2_DATA_COHERENCY_OWNED &&
+                    data->device_copies[d]->readers == 0)
+                    data->device_copies[d]->coherency_state = PB2_DATA_COHERENCY_SHARED;
+        }
+    }
+    return PB2_SUCCESS;
+}
+
+extern "C" int pb2_data_get_state(const pb2_data_t* data, int dev, pb2_data_state_t* out) {
+    if (!data || !out || dev < 1 || dev >= PB2_MAX_DEVICES) return PB2_ERR_BAD_PARAM;
+    const pb2_copy_t* c = data->device_copies[dev];
+    out->has_copy = c != nullptr;
+    out->dev_ptr = c ? c->device_private : nullptr;
+    out->dev_version = c ? c->version : 0;
+    out->dev_coherency = c ? c->coherency_state : (uint8_t)PB2_DATA_COHERENCY_INVALID;
+    out->readers = c ? c->readers : 0;
+    out->host_version = data->host_copy.version;
+    out->host_coherency = data->host_copy.coherency_state;
+    out->owner_device = data->owner_device;
+    return PB2_SUCCESS;
 }
 
 // ------------------------------------------------------------------------------------------ state-machine hooks

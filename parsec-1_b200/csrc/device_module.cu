@@ -67,6 +67,7 @@ struct pb2_device_s {
     std::atomic<int32_t> mutex{0};  // tasks inside the module (parsec_device_gpu_module_t.mutex)
     std::mutex pending_lock;
     std::deque<pb2_gpu_task_t*> pending;  // parsec_device_gpu_module_t.pending
+    std::deque<pb2_gpu_task_t*> deferred; // prefetches queued while nobody managed the device (not counted in mutex)
     // everything below is touched by the manager only
     cudaStream_t h2d = nullptr, d2h = nullptr;
     std::vector<cudaStream_t> exec;
@@ -96,6 +97,7 @@ struct pb2_device_s {
     };
     std::vector<Workspace> workspace;
     std::unordered_map<void*, size_t> registered;
+    pb2_device_hooks_t hooks = {nullptr, nullptr};
     std::vector<std::vector<cudaEvent_t>> launch_marks;  // profile_launches: completion marks per exec stream
 };
 
@@ -114,6 +116,44 @@ extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->trace_events = 0;
     p->profile_launches = 0;
     p->sort_pending_tasks = 0;
+    p->prefetch_deferred = 0;
+}
+
+// The reference's MCA parameters reach a process as environment variables PARSEC_MCA_<name> (parsec/utils/mca_param.c;
+// registered for this module in device_cuda_component.c:163-206).  Inside a PaRSEC build the overlay shim hands over
+// the values the runtime parsed; a host that drives the library directly gets the same names through this function.
+static bool env_int64(const char* name, int64_t* out) {
+    const char* v = getenv(name);
+    if (!v || !*v) return false;
+    char* end = nullptr;
+    long long x = strtoll(v, &end, 0);
+    if (end == v) return false;
+    *out = (int64_t)x;
+    return true;
+}
+
+extern "C" int pb2_device_params_from_env(pb2_device_params_t* p) {
+    if (!p) return PB2_ERR_BAD_PARAM;
+    int n = 0;
+    int64_t v;
+    if (env_int64("PARSEC_MCA_device_cuda_memory_use", &v) && v > 0 && v <= 100) { p->memory_use_percent = (int)v; ++n; }
+    if (env_int64("PARSEC_MCA_device_cuda_memory_block_size", &v) && v > 0) { p->memory_block_size = v; ++n; }
+    if (env_int64("PARSEC_MCA_device_cuda_memory_number_of_blocks", &v)) { p->memory_number_of_blocks = v; ++n; }
+    if (env_int64("PARSEC_MCA_device_cuda_max_streams", &v) && v >= 3) { p->max_streams = (int)v; ++n; }
+    if (env_int64("PARSEC_MCA_device_cuda_max_number_of_ejected_data", &v) && v > 0) { p->max_number_of_ejected_data = (int)v; ++n; }
+    if (env_int64("PARSEC_MCA_device_cuda_sort_pending_tasks", &v)) { p->sort_pending_tasks = v != 0; ++n; }
+    return n;
+}
+
+// device_cuda_enabled (-1 = every GPU, n = the first n) and device_cuda_mask (bit i = GPU i may be used),
+// device_cuda_component.c:165-172, :107.
+extern "C" int pb2_device_is_enabled(int cuda_index) {
+    int64_t enabled = -1, mask = -1;
+    env_int64("PARSEC_MCA_device_cuda_enabled", &enabled);
+    env_int64("PARSEC_MCA_device_cuda_mask", &mask);
+    if (cuda_index < 0 || cuda_index >= 63) return 0;
+    if (enabled >= 0 && cuda_index >= enabled) return 0;
+    return (mask >> cuda_index) & 1 ? 1 : 0;
 }
 
 static cudaEvent_t get_event(pb2_device_s* d) {
@@ -154,10 +194,19 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
                 cuda_index, count);
         return PB2_ERR_DEVICE;
     }
+    if (!params && !pb2_device_is_enabled(cuda_index)) {
+        fprintf(stderr, "[parsec_b200] CUDA device %d is disabled by PARSEC_MCA_device_cuda_enabled / _mask\n", cuda_index);
+        return PB2_ERR_NOT_SUPPORTED;
+    }
     PB2_CUDA_OK(cudaSetDevice(cuda_index));
     pb2_device_s* d = new pb2_device_s();
     d->cuda_index = cuda_index;
-    if (params) d->params = *params; else pb2_device_params_default(&d->params);
+    if (params) {
+        d->params = *params;
+    } else {  // no struct from the caller: the defaults, then the reference's PARSEC_MCA_device_cuda_* environment
+        pb2_device_params_default(&d->params);
+        pb2_device_params_from_env(&d->params);
+    }
     memset(&d->stats, 0, sizeof(d->stats));
     {
         std::lock_guard<std::mutex> g(g_devices_lock);
@@ -219,9 +268,30 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
 
 static void release_copy(pb2_device_s* d, pb2_copy_t* c) {  // detach + give the memory back
     CopyList::chop(c, d->lists);
-    if (c->original) c->original->device_copies[d->device_index] = nullptr;
+    pb2_data_s* original = c->original;
+    if (original) original->device_copies[d->device_index] = nullptr;
     if ((c->flags & PB2_FLAG_OWNED) && c->device_private) d->heap->free(c->device_private);
     delete c;
+    if (original && d->hooks.copy_released) d->hooks.copy_released(d, original, original->user);
+}
+
+extern "C" int pb2_device_set_hooks(pb2_device_t* d, const pb2_device_hooks_t* hooks) {
+    if (!d) return PB2_ERR_BAD_PARAM;
+    if (hooks) d->hooks = *hooks; else d->hooks = pb2_device_hooks_t{nullptr, nullptr};
+    return PB2_SUCCESS;
+}
+extern "C" int pb2_device_nb_streams(const pb2_device_t* d) { return d ? (int)d->exec.size() + 2 : 0; }
+extern "C" void* pb2_device_stream(const pb2_device_t* d, int index) {
+    if (!d || index < 0 || index >= (int)d->exec.size() + 2) return nullptr;
+    return index == 0 ? (void*)d->h2d : index == 1 ? (void*)d->d2h : (void*)d->exec[index - 2];
+}
+extern "C" int pb2_device_stream_index(const pb2_device_t* d, const void* cuda_stream) {
+    if (!d) return -1;
+    if (cuda_stream == (const void*)d->h2d) return 0;
+    if (cuda_stream == (const void*)d->d2h) return 1;
+    for (size_t i = 0; i < d->exec.size(); ++i)
+        if (cuda_stream == (const void*)d->exec[i]) return (int)i + 2;
+    return -1;
 }
 
 extern "C" int pb2_device_memory_release(pb2_device_t* d) {
@@ -315,6 +385,8 @@ extern "C" int pb2_device_get_stats(pb2_device_t* d, pb2_device_stats_t* out, in
     }
     return PB2_SUCCESS;
 }
+
+extern "C" const pb2_device_stats_t* pb2_device_stats_live(const pb2_device_t* d) { return d ? &d->stats : nullptr; }
 
 extern "C" int64_t pb2_device_get_events(pb2_device_t* d, pb2_event_t* out, int64_t max_events) {
     if (!d) return PB2_ERR_BAD_PARAM;
@@ -513,6 +585,15 @@ static bool start_w2r(pb2_device_s* d) {
     int limit = std::max(1, d->params.max_number_of_ejected_data);
     for (pb2_copy_t* c = d->owned_lru.head; c && (int)st->w2r_copies.size() < limit;) {
         pb2_copy_t* next = c->next;
+        if (c->readers == 0 && d->hooks.data_alive && c->original &&
+            !d->hooks.data_alive(d, c->original, c->original->user)) {
+            // the runtime destroyed this data while its last version was still on the device (a NEW tile nobody reads
+            // back): its host memory is gone, there is nothing to write back to
+            release_copy(d, c);
+            d->stats.nb_evictions++;
+            c = next;
+            continue;
+        }
         if (c->readers == 0) {
             CopyList::chop(c, d->lists);
             c->readers++;
@@ -766,12 +847,10 @@ extern "C" int pb2_kernel_scheduler(pb2_device_t* d, pb2_gpu_task_t* task) {
 // task of a taskpool would run alone.  No counterpart in the reference (its workers submit concurrently).
 extern "C" int pb2_device_hold(pb2_device_t* d) {
     if (!d) return 0;
-    int32_t rc = d->mutex.fetch_add(1);
-    if (rc > 0) {
-        d->mutex.fetch_sub(1);
-        return 0;
-    }
-    return 1;
+    // A failed attempt must never move the counter: an increment followed by a decrement could land around the active
+    // manager's last completion, which would then see 2 instead of 1 and never notice that the device has drained.
+    int32_t expected = 0;
+    return d->mutex.compare_exchange_strong(expected, 1) ? 1 : 0;
 }
 extern "C" int pb2_device_manage(pb2_device_t* d) {
     if (!d) return PB2_ERR_BAD_PARAM;
@@ -801,6 +880,11 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
         }
         if (cur == nullptr && d->inflight_count < max_inflight) {
             std::lock_guard<std::mutex> g(d->pending_lock);
+            while (!d->deferred.empty()) {  // queued while nobody managed the device: they count from now on
+                d->mutex.fetch_add(1);
+                d->pending.push_back(d->deferred.front());
+                d->deferred.pop_front();
+            }
             if (!d->pending.empty()) {
                 size_t pick = 0;
                 if (d->params.sort_pending_tasks) {
@@ -913,6 +997,22 @@ extern "C" int pb2_device_data_advise(pb2_device_t* d, pb2_data_t* data, int adv
             t->flow_nb_elts[0] = data->nb_elts;
             t->trace_dc[0] = (int32_t)data->dc_id;
             t->locals[2] = -1;
+            if (d->params.prefetch_deferred) {
+                // only queue: join the running manager's count if there is one, else wait for the next manager
+                int32_t cur = d->mutex.load();
+                while (true) {
+                    if (cur == 0) {
+                        std::lock_guard<std::mutex> g(d->pending_lock);
+                        d->deferred.push_back(t);
+                        return PB2_SUCCESS;
+                    }
+                    if (d->mutex.compare_exchange_weak(cur, cur + 1)) {
+                        std::lock_guard<std::mutex> g(d->pending_lock);
+                        d->pending.push_back(t);
+                        return PB2_SUCCESS;
+                    }
+                }
+            }
             int rc = pb2_kernel_scheduler(d, t);
             return rc == PB2_HOOK_RETURN_ASYNC ? PB2_SUCCESS : PB2_ERROR;
         }
@@ -931,9 +1031,9 @@ extern "C" int pb2_device_data_advise(pb2_device_t* d, pb2_data_t* data, int adv
     }
 }
 
-// ------------------------------------------------------------------------------------ zone heap test hooks
-// parsec/utils/zone_malloc.h:41-63.  Exposed so that the heap's placement decisions can be compared with the
-// reference allocator offset by offset (tests/test_cabi_host.py) without a GPU.
+// ------------------------------------------------------------------------------------ heap test hooks
+// The interface of parsec/utils/zone_malloc.h:41-63 over pb2::ZoneHeap.  Exposed so that the heap's invariants can be
+// checked without a GPU (tests/test_cabi_host.py).
 extern "C" void* pb2_zone_create(int max_segment, size_t unit_size) {
     if (max_segment <= 0 || unit_size == 0) return nullptr;
     return new ZoneHeap((char*)(uintptr_t)(1ull << 40), max_segment, unit_size);

@@ -7,6 +7,7 @@
 
 #include <atomic>
 #include <deque>
+#include <map>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -52,6 +53,7 @@ struct pb2_data_s {
     size_t host_pitch = 0, dev_pitch = 0;
     pb2_copy_t host_copy;
     pb2_copy_t* device_copies[PB2_MAX_DEVICES] = {nullptr};
+    void* user = nullptr;  // pb2_data_set_user: the overlay shim keeps its parsec_data_copy_t here
 };
 
 namespace pb2 {
@@ -60,26 +62,35 @@ namespace pb2 {
 int data_start_transfer_ownership(pb2_data_s* data, int device, uint8_t access);
 void data_end_transfer_ownership(pb2_data_s* data, int device, uint8_t access);
 
-// HBM heap: first-fit over fixed-size units, same policy as parsec/utils/zone_malloc.c
+// HBM heap over one cudaMalloc, in units of `unit` bytes.  Plays the part of parsec/utils/zone_malloc.c for the device
+// module (one allocation carved into tiles) with a policy of its own, built for what a tile cache does: nearly every
+// request is one of one or two tile sizes, and a freed tile is wanted again at once by the task that evicted it.
+//   * free(p) pushes the extent on a LIFO stack of extents of exactly its size: O(1), no merging;
+//   * alloc(size) pops that stack: O(1); if it is empty the extent is carved from the lowest-addressed run of the
+//     coalesced free space (an ordered map offset -> length);
+//   * only when that fails too are the stacks emptied into the map, where neighbours merge, and the carve retried --
+//     the one place where extents of different sizes meet (a taskpool with other tile sizes has started).
+// in_use() is a counter.
 class ZoneHeap {
 public:
-    ZoneHeap(char* base, int max_segment, size_t unit);
+    ZoneHeap(char* base, int nb_units, size_t unit);
     void* alloc(size_t size);
     bool free(void* p);
-    size_t in_use() const;
-    size_t capacity() const { return unit_ * (size_t)nseg_; }
+    size_t in_use() const { return used_units_ * unit_; }
+    size_t capacity() const { return unit_ * (size_t)nunits_; }
     char* base() const { return base_; }
     int64_t offset_of(const void* p) const { return (const char*)p - base_; }
 
 private:
-    struct Seg {
-        int busy, units, before;
-    };
-    Seg* at(int id) { return (id < 0 || id >= nseg_) ? nullptr : &seg_[id]; }
+    bool carve(uint32_t want, uint32_t* at);
+    void merge_in(uint32_t at, uint32_t len);
     char* base_;
-    std::vector<Seg> seg_;
-    int nseg_, cursor_;
+    uint32_t nunits_;
     size_t unit_;
+    size_t used_units_ = 0;
+    std::vector<uint32_t> len_at_;                                // units of the live extent starting here, 0 = none
+    std::map<uint32_t, uint32_t> runs_;                           // coalesced free space: first unit -> units
+    std::unordered_map<uint32_t, std::vector<uint32_t>> parked_;  // freed extents by size, not merged yet
 };
 
 struct CopyList {  // parsec_list_t of data copies, LRU order: front = oldest

@@ -24,7 +24,8 @@ class DeviceParams(C.Structure):
     _fields_ = [("memory_use_percent", C.c_int), ("memory_block_size", C.c_int64),
                 ("memory_number_of_blocks", C.c_int64), ("max_streams", C.c_int),
                 ("max_number_of_ejected_data", C.c_int), ("max_inflight_tasks", C.c_int), ("trace_events", C.c_int),
-                ("profile_launches", C.c_int), ("sort_pending_tasks", C.c_int)]
+                ("profile_launches", C.c_int), ("sort_pending_tasks", C.c_int),
+                ("prefetch_deferred", C.c_int)]
 
 
 class DeviceStats(C.Structure):

@@ -14,11 +14,12 @@
     } while (0)
 
 int main(void) {
-    /* HBM heap hooks: zone_malloc_init / zone_malloc / zone_free (parsec/utils/zone_malloc.h:41-63) */
+    /* HBM heap hooks (the job of zone_malloc_init / zone_malloc / zone_free, parsec/utils/zone_malloc.h:41-63) */
     void* z = pb2_zone_create(8, 4096);
     CHECK(z != NULL);
     int64_t a = pb2_zone_malloc(z, 4096), b = pb2_zone_malloc(z, 3 * 4096);
-    CHECK(a == 0 && b == 4096 && pb2_zone_in_use(z) == 4 * 4096);
+    CHECK(a >= 0 && b >= 0 && a % 4096 == 0 && b % 4096 == 0 && (a + 4096 <= b || b + 3 * 4096 <= a));
+    CHECK(pb2_zone_in_use(z) == 4 * 4096);
     CHECK(pb2_zone_free(z, a) == PB2_SUCCESS && pb2_zone_malloc(z, 5 * 4096) == -1);
     pb2_zone_destroy(z);
 

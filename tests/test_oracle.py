@@ -276,3 +276,29 @@ def test_generator_matches_reference_initialize_tile_golden():
         O.lib().orc_init_tile(tile.ctypes.data, c["m"], c["n"], c["mb"], c["nb"], c["M"], c["ld"], c["seed"])
         want = np.array([float.fromhex(v) for v in c["values"]])
         assert np.array_equal(tile, want), c
+
+
+def test_oracle_matches_the_reference_runtime_golden():
+    """tests/golden/dag_reference_runtime.json was recorded from the reference RUNTIME itself (unmodified libparsec.so,
+    the dgemm_NN JDF through parsec-ptgpp, CPU bodies; tests/golden/make_dag_golden.py).  The oracle reproduces its
+    per-class task counts, the final version of every tile's host copy, and C bit for bit (SHA-256)."""
+    import hashlib
+    golden = json.load(open(os.path.join(HERE, "golden", "dag_reference_runtime.json")))
+    assert len(golden) >= 5
+    for g in golden:
+        M, N, K, NB, runs = g["M"], g["N"], g["K"], g["NB"], g["runs"]
+        dA = O.bc(0, NB, NB, M, K, 0, 0, M, K)
+        dB = O.bc(0, NB, NB, K, N, 0, 0, K, N)
+        dC = O.bc(0, NB, NB, M, N, 0, 0, M, N)
+        A, B, Cm = O.fill(dA, 1789), O.fill(dB, 1805), O.fill(dC, 1901)
+        gemm = read_a = read_b = 0
+        versions = np.zeros(dC.mt * dC.nt, dtype=np.int64)
+        for _ in range(runs):
+            cnt, ver = O.tiled_dgemm(M, N, K, NB, NB, NB, A, B, Cm)
+            gemm, read_a, read_b = gemm + cnt.gemm, read_a + cnt.read_a, read_b + cnt.read_b
+            versions += ver                                   # a second taskpool starts from the versions of the first
+        assert {"read_a": read_a, "read_b": read_b, "gemm": gemm} == g["counts"]
+        assert versions.tolist() == g["versions"]["C"]
+        assert not any(g["versions"]["A"]) and not any(g["versions"]["B"])
+        assert len(g["versions"]["A"]) == dA.mt * dA.nt and len(g["versions"]["B"]) == dB.mt * dB.nt
+        assert hashlib.sha256(Cm.tobytes()).hexdigest() == g["c_sha256"]
