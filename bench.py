@@ -3,7 +3,7 @@
 pipeline (stage-in -> hand-written sm_100a tile kernel -> stage-out, HBM tile cache).
 
     python bench.py --gpus 1 --steps 3 --warmup 3            # our arm
-    python bench.py --impl reference --steps 1 --warmup 0    # CPU arm: the oracle port on the host cores
+    python bench.py --impl reference --steps 1 --warmup 0    # CPU arm: the reference runtime with CPU bodies on the host cores
 
 One JSON line on stdout (rank 0).  A "step" is one full tiled DGEMM over the workload's matrices.
   value : GFLOP/s with every tile already resident in the HBM cache when the timed region starts
@@ -85,26 +85,61 @@ def cpu_port_gflops(n, nb, threads):
     return 2.0 * n ** 3 / dt * 1e-9, dt
 
 
+def reference_runtime_gflops(n, nb, threads):
+    """The reference's own CPU path for this workload: the unmodified reference runtime (baseline/_ref/stock/libparsec.so,
+    built from /root/reference by overlay/build_overlay.sh) executing the dgemm_NN JDF (parsec-ptgpp) with CPU task
+    bodies on `threads` cores, --mca device_cuda_enabled 0.  The reference ships no tile GEMM (its CPU body calls an
+    un-vendored cblas_dgemm), so the body's tile routine is the oracle's blocked plain-C one, handed in with --cpu-tile.
+    Returns (GFLOP/s, seconds) or None when the binaries are not there."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    app = os.path.join(ref, "bin", "dgemm_NN_app")
+    if not (os.path.exists(app) and os.path.exists(os.path.join(ref, "stock", "libparsec.so.4"))):
+        return None
+    env = dict(os.environ, LD_LIBRARY_PATH=os.pathsep.join([os.path.join(ref, "stock"), os.environ.get("LD_LIBRARY_PATH", "")]))
+    cmd = [app, "-N", str(n), "-t", str(nb), "-c", str(threads), "--cpu-tile",
+           os.path.join(ROOT, "oracle", "liboracle.so") + ":orc_dgemm_tile", "--", "--mca", "device_cuda_enabled", "0"]
+    try:
+        p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1800)
+        line = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
+    except Exception:
+        return None
+    if p.returncode != 0 or line.get("gemm_cpu") != (n // nb) ** 3:
+        return None
+    return line["gflops_best"], line["seconds_best"]
+
+
+def cpu_baseline(n, nb, threads):
+    """cpu_baseline object: the reference runtime with CPU bodies when it is built, else the oracle port."""
+    r = reference_runtime_gflops(n, nb, threads)
+    if r is not None:
+        return {"value": r[0], "unit": "GFLOP/s", "cores": threads, "kind": "reference",
+                "sample": "tiled DGEMM N=%d NB=%d (%.1f s): the reference runtime (unmodified libparsec, dgemm_NN JDF through "
+                          "parsec-ptgpp) with CPU task bodies; tile routine = the oracle's blocked plain C" % (n, nb, r[1])}, r[1]
+    g, dt = cpu_port_gflops(n, nb, threads)
+    return {"value": g, "unit": "GFLOP/s", "cores": threads, "kind": "port",
+            "sample": "tiled DGEMM N=%d NB=%d (%.1f s), oracle port with OpenMP (baseline/_ref not built)" % (n, nb, dt)}, dt
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     n, nb = args.cpu_n, args.nb
     for _ in range(args.warmup):
-        cpu_port_gflops(min(n, 2 * nb), nb, threads)
-    vals, secs = [], []
+        cpu_baseline(min(n, 2 * nb), nb, threads)
+    vals, secs, base = [], [], None
     for _ in range(max(1, args.steps)):
-        g, dt = cpu_port_gflops(n, nb, threads)
-        vals.append(g)
+        base, dt = cpu_baseline(n, nb, threads)
+        vals.append(base["value"])
         secs.append(dt)
     v = sum(vals) / len(vals)
-    sample = "tiled DGEMM N=%d NB=%d (same tile size, reduced N) per step, oracle port with OpenMP" % (n, nb)
+    base = dict(base, value=v)
     print(json.dumps({
         "impl": "reference", "metric": "tiled GEMM GFLOP/s", "value": v, "unit": "GFLOP/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "tiled DGEMM N=%d NB=%d fp64 via CPU task bodies" % (args.n, nb), "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "GFLOP/s", "cores": threads, "kind": "port", "sample": sample},
+        "config": {"workload": "tiled DGEMM N=%d NB=%d fp64 via CPU task bodies" % (args.n, nb), "sample": base["sample"]},
+        "cpu_baseline": base,
         "e2e": {"value": v, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -131,6 +166,138 @@ def fp64_peak_tflops(torch):
     return 2.0 * n ** 3 / (best * 1e-3) * 1e-12
 
 
+def parity_check(H, torch, dist, dev, bufs, mtypes, N, NB, P, Q, grid_rank, rank, world, knobs, bf16, vectors=4):
+    """One extra step from freshly generated inputs, checked without the oracle and without our kernels:
+      * Freivalds: for `vectors` random +-1 vectors X, C1 X must equal C0 X + A (B X); every rank multiplies the tiles it
+        owns (torch on the GPU, fp64), partial products are summed over the ranks;
+      * two C tiles per rank recomputed as C0 + sum_k A(m,k) B(k,n) with torch.matmul in fp64 (cuBLAS), operand tiles
+        fetched from their owners with torch.distributed broadcasts;
+      * every owned C tile's host copy must end at version KT.
+    Both residuals are scaled like the north-star norm, ||.||inf / (||A||inf ||B||inf N eps), eps = 2^-53 (fp64) or
+    2^-24 (fp32 accumulation of bf16 products); the worst over ranks is reported."""
+    L = H.lib()
+    T = N // NB
+    assert T * NB == N
+    cuda = torch.device("cuda", torch.cuda.current_device())
+    tdt = {H.MATRIX_DOUBLE: torch.float64, H.MATRIX_FLOAT: torch.float32, H.MATRIX_BF16: torch.bfloat16}
+    mats = []
+    for seed, mtype, b in zip((1789, 1805, 1901), mtypes, bufs):
+        m = H.Matrix(mtype, N, N, NB, NB, P, Q, grid_rank)     # fresh descriptors: versions start at 0
+        m.set_buffer(b)
+        m.fill_lcg(seed, dev)
+        mats.append(m)
+    host = [b[:m.nbytes].view(tdt[mt]) for b, m, mt in zip(bufs, mats, mtypes)]
+    bs = NB * NB
+
+    def owned_columns(mat):
+        """{n: [(m, pos), ...] sorted by position}: the tiles of tile column n this rank stores."""
+        cols = {}
+        for n in range(T):
+            for m in range(T):
+                if L.pb2_matrix_rank_of(mat.h, m, n) == grid_rank:
+                    cols.setdefault(n, []).append((m, int(L.pb2_matrix_position(mat.h, m, n))))
+        for n in cols:
+            cols[n].sort(key=lambda t: t[1])
+        return cols
+
+    cols = [owned_columns(m) for m in mats]
+
+    def allsum(t):
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t
+
+    def matvec(i, X):
+        """(M X, row sums of |M|) over the tiles of matrix i this rank owns, summed over the ranks."""
+        Y = torch.zeros(N, X.shape[1], dtype=torch.float64, device=cuda)
+        rows = torch.zeros(N, dtype=torch.float64, device=cuda)
+        for n, tiles in cols[i].items():
+            Xn = X[n * NB:(n + 1) * NB]
+            for c0 in range(0, len(tiles), 32):
+                chunk = tiles[c0:c0 + 32]
+                if all(chunk[j + 1][1] == chunk[j][1] + 1 for j in range(len(chunk) - 1)):
+                    slab = host[i][chunk[0][1] * bs:(chunk[-1][1] + 1) * bs].to(cuda, non_blocking=True)
+                else:
+                    slab = torch.cat([host[i][p * bs:(p + 1) * bs] for _, p in chunk]).to(cuda, non_blocking=True)
+                slab = slab.view(len(chunk), NB, NB).to(torch.float64)       # [tile][column j][row i]
+                part = torch.einsum("cji,jr->cir", slab, Xn)
+                rs = slab.abs().sum(dim=1)
+                for j, (m, _) in enumerate(chunk):
+                    Y[m * NB:(m + 1) * NB] += part[j]
+                    rows[m * NB:(m + 1) * NB] += rs[j]
+        return allsum(Y), allsum(rows)
+
+    def tile(i, pos):
+        return host[i][pos * bs:(pos + 1) * bs].to(cuda).view(NB, NB).to(torch.float64).t()   # [row i][column j]
+
+    g = torch.Generator(device="cpu")
+    g.manual_seed(11)
+    X = (torch.randint(0, 2, (N, vectors), generator=g).to(torch.float64) * 2.0 - 1.0).to(cuda)
+    c0x, _ = matvec(2, X)
+    # sampled tiles: the first and the last C tile each rank stores
+    my_c = sorted((pos, m, n) for n, tiles in cols[2].items() for m, pos in tiles)
+    picks_mine = [my_c[0], my_c[-1]] if len(my_c) > 1 else my_c
+    c0_tiles = {(m, n): tile(2, pos) for pos, m, n in picks_mine}
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, [(m, n) for _, m, n in picks_mine])
+    else:
+        gathered = [[(m, n) for _, m, n in picks_mine]]
+
+    st = H.tiled_gemm(mats[0], mats[1], mats[2], dev, **knobs)
+
+    eps = 2.0 ** -24 if bf16 else 2.0 ** -53
+    bx, rows_b = matvec(1, X)
+    abx, rows_a = matvec(0, bx)
+    c1x, _ = matvec(2, X)
+    scale = float(rows_a.max()) * float(rows_b.max()) * N * eps
+    freivalds = float((c1x - c0x - abx).abs().max()) / scale
+    changed = float((c1x - c0x).abs().max()) > 1.0
+    pos_of = lambda i, m, n: int(L.pb2_matrix_position(mats[i].h, m, n))
+    tile_norm, nb_tiles = 0.0, 0
+    for owner, picks in enumerate(gathered):
+        for (m, n) in picks:
+            acc = c0_tiles[(m, n)].clone() if owner == rank else None
+            a_rows = torch.zeros(NB, dtype=torch.float64, device=cuda)
+            b_cols = torch.zeros(NB, dtype=torch.float64, device=cuda)
+            for k in range(T):
+                ops = []
+                for i, (tm, tn) in ((0, (m, k)), (1, (k, n))):
+                    src = int(L.pb2_matrix_rank_of(mats[i].h, tm, tn))
+                    t = tile(i, pos_of(i, tm, tn)).contiguous() if src == grid_rank else \
+                        torch.empty(NB, NB, dtype=torch.float64, device=cuda)
+                    if world > 1:
+                        dist.broadcast(t, src=src)
+                    ops.append(t)
+                if owner == rank:
+                    acc += ops[0] @ ops[1]
+                    a_rows += ops[0].abs().sum(dim=1)
+                    b_cols += ops[1].abs().sum(dim=0)
+            if owner == rank:
+                got = tile(2, pos_of(2, m, n))
+                err = float((got - acc).abs().sum(dim=1).max())
+                tile_norm = max(tile_norm, err / (float(a_rows.max()) * float(b_cols.max()) * N * eps))
+                nb_tiles += 1
+    versions_ok = all(mats[2].version(m, n) == T for n, tiles in cols[2].items() for m, _ in tiles)
+    owned_c = sum(len(t) for t in cols[2].values())
+    counts_ok = st["nb_gemm"] == owned_c * T
+    res = torch.tensor([freivalds, tile_norm, 0.0 if (versions_ok and counts_ok and changed) else 1.0, float(nb_tiles)],
+                       dtype=torch.float64, device=cuda)
+    if world > 1:
+        worst = res.clone()
+        dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+        total = res.clone()
+        dist.all_reduce(total, op=dist.ReduceOp.SUM)
+        res = torch.stack([worst[0], worst[1], worst[2], total[3]])
+    for m in mats:
+        m.close()
+    fr, tn, bad, nt = [float(x) for x in res.tolist()]
+    return {"norm": max(fr, tn), "freivalds_norm": fr, "tile_norm": tn, "tiles": int(nt), "vectors": vectors,
+            "versions_ok": bad == 0.0, "eps": "2^-24" if bf16 else "2^-53", "bound": 10.0,
+            "how": "one extra step from fresh inputs: Freivalds with +-1 vectors and sampled C tiles recomputed with "
+                   "torch fp64 (cuBLAS), scaled as ||.||inf / (||A||inf ||B||inf N eps); task counts and C versions == KT"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -146,6 +313,7 @@ def main():
     ap.add_argument("--streams", type=int, default=18, help="h2d + d2h + exec streams (the module spreads a task over as "
                     "many exec streams as its tile size needs: 5 at NB=1024, 16 at NB=512)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the extra checked step after the timed regions")
     ap.add_argument("--hbm-gib", type=float, default=0.0,
                     help="cap the HBM tile heap (GiB) to run out of core: the BASELINE configs[3] mechanism (LRU evict + "
                          "write-back) at a size the box's host memory allows; 0 = 95%% of free HBM")
@@ -196,9 +364,19 @@ def main():
         except Exception:
             peak_tf, peak_src = 1590.0, "B200_PROFILING.md fallback 1.59 PFLOP/s (of fallback)"
     else:
-        peak_tf = fp64_peak_tflops(torch)
-        peak_src = ("measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10; MEASURED_PEAKS.json has no fp64 entry "
-                    "(DMMA issue peak measured 37.1 TFLOP/s, profiles/microbench_r1_v2_tma.log)")
+        # MEASURED_PEAKS.json has no FP64 entry.  profiles/fp64_peak_r2.json is the same measurement for FP64 taken on
+        # this pool's B200 (parsec-1_b200/tools/fp64_peak.py: cuBLAS 8192^3, best of 10 and ~4 s sustained, clocks
+        # recorded); the tile kernel is timed inside a seconds-long step, so it is compared with the sustained figure.
+        # The live number of this very run is reported next to it.
+        live_tf = fp64_peak_tflops(torch)
+        try:
+            pk = json.load(open(os.path.join(ROOT, "profiles", "fp64_peak_r2.json")))
+            peak_tf = float(pk["fp64_tflops_sustained"])
+            peak_src = ("profiles/fp64_peak_r2.json fp64_tflops_sustained (cuBLAS DGEMM 8192^3, ~4 s of back-to-back launches, "
+                        "of measured); burst %.2f; live in this run %.2f" % (float(pk["fp64_tflops_burst"]), live_tf))
+        except Exception:
+            peak_tf = live_tf
+            peak_src = "measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10 (profiles/fp64_peak_r2.json missing)"
     hbm = {"memory_number_of_blocks": int(args.hbm_gib * 2048)} if args.hbm_gib > 0 else {}   # 512 KiB blocks
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0, **hbm)
     mats, bufs = [], []
@@ -226,8 +404,8 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(nsteps):
-            if flush:
-                H.lib().pb2_device_memory_release(dev.h)
+            if flush and H.lib().pb2_device_memory_release(dev.h) != H.SUCCESS:
+                raise SystemExit("pb2_device_memory_release refused: the e2e steps would run from a warm cache")
             H.tiled_gemm(A, B, Cm, dev, **knobs)
         e1.record()
         barrier()
@@ -283,6 +461,13 @@ def main():
         achieved_tf = per_launch_flops * nstreams / (avg_ms * 1e-3) * 1e-12
         prof = {"avg_launch_ms": avg_ms, "samples": int(len(lms)), "resident_launches": nstreams}
 
+    parity = None
+    if not args.no_parity and not args.replicas:
+        for m in mats:
+            m.close()
+        mats = []
+        parity = parity_check(H, torch, dist if world > 1 else None, dev, bufs, mtypes, N, NB, P, Q, grid_rank, rank, world,
+                              knobs, bf16)
     if args.replicas:
         flops *= world
     value = flops / (ms_resident * 1e-3) * 1e-9          # whole job: one N x N x N product spread over all ranks
@@ -319,18 +504,20 @@ def main():
         "host_us_per_task": {"submit": st_resident["host_submit_ns"] / 1e3 / max(1, st_resident["kernel_launches"]),
                              "retire": st_resident["host_retire_ns"] / 1e3 / max(1, st_resident["kernel_launches"])},
         "clocks": clocks,
+        "parity": parity,
         "roofline": {"bound": "tensor", "achieved": achieved_tf if prof else None, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": (achieved_tf / peak_tf) if prof else None,
+                     # FP64 only: against the DMMA issue rate, 148 SMs x 128 flop per clock (one DMMA.8x8x4 per 16
+                     # cycles per sub-partition), at the SM clock sampled during the timed region
+                     "frac_of_dmma_issue_peak": (achieved_tf / (148 * 128 * clocks["sm_mhz"] * 1e-6))
+                     if (prof and not bf16 and clocks and clocks.get("sm_mhz")) else None,
                      # dram bytes per launch from one ncu --set full capture (profiles/dgemm_tma_r1_ncu.md)
                      "traffic": 25206528 if (not bf16 and NB == 1024) else None,
                      "kernel": "pb2::gemm_umma_pair" if bf16 else "pb2::dgemm_nn_tma", "peak_source": peak_src,
                      "detail": prof, "algorithmic_flops_per_launch": per_launch_flops},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:   # the CPU baseline is a single-GPU-run figure (N = 1 only)
-        threads = os.cpu_count() or 1
-        g, dt = cpu_port_gflops(args.cpu_n, NB, threads)
-        out["cpu_baseline"] = {"value": g, "unit": "GFLOP/s", "cores": threads, "kind": "port",
-                               "sample": "tiled DGEMM N=%d NB=%d (%.1f s), oracle port with OpenMP" % (args.cpu_n, NB, dt)}
+        out["cpu_baseline"], _ = cpu_baseline(args.cpu_n, NB, os.cpu_count() or 1)
     for m in mats:
         m.close()
     dev.close()

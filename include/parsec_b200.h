@@ -163,6 +163,9 @@ typedef struct pb2_device_params_s {
     int prefetch_deferred;        /* 1: a PREFETCH advice given while nobody manages the device is only queued, like the
                                      reference's push to `pending` (device_cuda_module.c:1668); the next manager runs it.
                                      0 (default): the adviser drives the device until the prefetch is done */
+    int use_priorities;           /* 1: the pending list hands out the task with the highest priority first (oldest first
+                                     among equals), as the reference's priority-ordered lists do (PARSEC_GPU_USE_PRIORITIES,
+                                     device_cuda_module.c:1683-1692); 0 (default): first come, first served */
 } pb2_device_params_t;
 void pb2_device_params_default(pb2_device_params_t* p);
 /* The reference's MCA parameter names, as they reach a process in its environment (PARSEC_MCA_<name>,
@@ -199,6 +202,9 @@ typedef struct pb2_device_hooks_s {
     int (*data_alive)(pb2_device_t* dev, pb2_data_t* data, void* user);
 } pb2_device_hooks_t;
 int pb2_device_set_hooks(pb2_device_t* dev, const pb2_device_hooks_t* hooks);
+/* Give back the HBM of `data`'s copy on this device (the runtime has destroyed the data; what the reference's LRU flush
+ * does to detached copies, device_cuda_module.c:803-820).  The device must be idle or held by the caller (pb2_device_hold). */
+int pb2_device_drop_copy(pb2_device_t* dev, pb2_data_t* data);
 /* The module's CUDA streams, numbered like parsec_device_gpu_module_t.exec_stream[] (device_cuda_module.c:414-420):
  * 0 = h2d, 1 = d2h, 2.. = exec.  pb2_device_stream_index maps the cuda_stream a submit / stage callback received
  * back to that number (-1 = not one of ours). */
@@ -213,6 +219,9 @@ typedef struct pb2_device_stats_s {
     uint64_t nb_evictions, nb_w2r_tasks, nb_w2r_tiles, nb_stalls, kernel_launches;
     uint64_t hbm_bytes_total, hbm_bytes_in_use;
     uint64_t host_submit_ns, host_retire_ns; /* manager-thread time spent submitting / retiring tasks */
+    uint64_t nb_cleanouts;                   /* tasks whose stage-in was taken back (parsec_cuda_kernel_cleanout) */
+    uint64_t data_in_from_device[PB2_MAX_DEVICES]; /* bytes staged in, by source device (parsec_device_module_t.data_in_from_device,
+                                                device.h:130): [0] = host, [i >= 2] = the peer GPU with that device index */
 } pb2_device_stats_t;
 int pb2_device_get_stats(pb2_device_t* dev, pb2_device_stats_t* out, int reset);
 /* the live counters, for a caller on the manager thread that folds them into its own after every task (the overlay

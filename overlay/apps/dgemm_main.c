@@ -13,7 +13,7 @@
  * the overlay libparsec (overlay/device_cuda_b200_shim.c + libparsec_b200.so); the library is chosen at run time
  * (LD_LIBRARY_PATH), nothing here knows which one it got.
  *
- * usage: dgemm_NN_app [-N n | -M m -n n -K k] [-t nb] [-c cores] [-r runs] [--cublas] [--dump file] [--release]
+ * usage: dgemm_NN_app [-N n | -M m -n n -K k] [-t nb] [-c cores] [-r runs] [--cublas] [--dump file] [--release] [--decline k]
  *                     [--versions file.json] [--cpu-tile lib.so:symbol] [-- parsec/MCA arguments]
  */
 #include "parsec.h"
@@ -116,7 +116,7 @@ static double now(void)
 
 int main(int argc, char **argv)
 {
-    int M = 2048, N = 2048, K = 2048, NB = 256, cores = -1, runs = 1, use_cublas = 0, release = 0;
+    int M = 2048, N = 2048, K = 2048, NB = 256, cores = -1, runs = 1, use_cublas = 0, release = 0, decline_k = -1;
     const char *dump = NULL, *cpu_tile_spec = NULL, *versions_path = NULL;
     dgemm_cpu_tile_t cpu_tile = NULL;
     int pargc = 1;
@@ -133,6 +133,7 @@ int main(int argc, char **argv)
         else if( !strcmp(argv[i], "-r") && i + 1 < argc ) runs = atoi(argv[++i]);
         else if( !strcmp(argv[i], "--cublas") ) use_cublas = 1;
         else if( !strcmp(argv[i], "--release") ) release = 1;
+        else if( !strcmp(argv[i], "--decline") && i + 1 < argc ) decline_k = atoi(argv[++i]);
         else if( !strcmp(argv[i], "--dump") && i + 1 < argc ) dump = argv[++i];
         else if( !strcmp(argv[i], "--cpu-tile") && i + 1 < argc ) cpu_tile_spec = argv[++i];
         else if( !strcmp(argv[i], "--versions") && i + 1 < argc ) versions_path = argv[++i];
@@ -182,7 +183,7 @@ int main(int argc, char **argv)
     for( int r = 0; r < runs; r++ ) {
         if( release ) parsec_devices_release_memory();   /* start every run with an empty device cache */
         parsec_dgemm_NN_taskpool_t *tp = parsec_dgemm_NN_new(&dcA->super, &dcB->super, &dcC->super, CuHI, use_cublas,
-                                                             cpu_tile);
+                                                             cpu_tile, decline_k);
         parsec_add2arena(&tp->arenas_datatypes[PARSEC_dgemm_NN_DEFAULT_ADT_IDX], parsec_datatype_double_t,
                          PARSEC_MATRIX_FULL, 1, NB, NB, NB, PARSEC_ARENA_ALIGNMENT_SSE, -1);
         double t0 = now();
@@ -195,9 +196,14 @@ int main(int argc, char **argv)
         parsec_del2arena(&tp->arenas_datatypes[PARSEC_dgemm_NN_DEFAULT_ADT_IDX]);
         parsec_taskpool_free(&tp->super);
     }
+    uint64_t d2d_bytes = 0, h2d_bytes = 0, d2h_bytes = 0;
     for( int d = 0; d < (int)parsec_nb_devices; d++ ) {
         parsec_device_module_t *dev = parsec_mca_device_get(d);
-        if( NULL != dev && PARSEC_DEV_CUDA == dev->type ) executed_on_gpu += dev->executed_tasks;
+        if( NULL == dev || PARSEC_DEV_CUDA != dev->type ) continue;
+        executed_on_gpu += dev->executed_tasks;
+        d2h_bytes += dev->data_out_to_host;
+        for( int j = 0; j < (int)dev->data_in_array_size; j++ )   /* bytes staged in, by source device (device.h:130) */
+            if( j >= 2 ) d2d_bytes += dev->data_in_from_device[j]; else h2d_bytes += dev->data_in_from_device[j];
     }
 
     /* versions of the host copies of C (KT per run) and of A, B (0) */
@@ -253,11 +259,12 @@ int main(int argc, char **argv)
     printf("{\"M\": %d, \"N\": %d, \"K\": %d, \"NB\": %d, \"runs\": %d, \"cores\": %d, \"gpus\": %d, \"cublas\": %d, "
            "\"seconds_best\": %.6f, \"seconds_first\": %.6f, \"gflops_best\": %.3f, \"gflops_first\": %.3f, "
            "\"read_a\": %lld, \"read_b\": %lld, \"gemm_cpu\": %lld, \"gemm_gpu\": %lld, \"device_executed_tasks\": %llu, "
-           "\"c_version_min\": %u, \"c_version_max\": %u, \"ab_version_max\": %u}\n",
+           "\"c_version_min\": %u, \"c_version_max\": %u, \"ab_version_max\": %u, "
+           "\"h2d_bytes\": %llu, \"d2d_bytes\": %llu, \"d2h_bytes\": %llu}\n",
            M, N, K, NB, runs, parsec->virtual_processes[0]->nb_cores, nb_gpus, use_cublas, best, first,
            flops / best * 1e-9, flops / first * 1e-9, (long long)dgemm_NN_count[0], (long long)dgemm_NN_count[1],
            (long long)dgemm_NN_count[2], (long long)dgemm_NN_count[3], (unsigned long long)executed_on_gpu,
-           vmin, vmax, vab);
+           vmin, vmax, vab, (unsigned long long)h2d_bytes, (unsigned long long)d2d_bytes, (unsigned long long)d2h_bytes);
     fflush(stdout);
 
     for( int d = 0; d < (int)parsec_nb_devices; d++ ) {

@@ -72,6 +72,16 @@ void parsec_gpu_enable_debug(void)
  * ---------------------------------------------------------------------------------------------------------- */
 struct b200_module_s;
 
+/* One pb2_data_t mirrors one parsec_data_t for ALL the GPUs of the process (it holds one device copy per GPU, which is
+ * what lets a tile be staged from a peer GPU instead of the host); `copy` is indexed by the device index inside
+ * libparsec_b200. */
+struct b200_copy_s;
+typedef struct b200_mirror_s {
+    pb2_data_t         *data;
+    struct b200_copy_s *copy[PB2_MAX_DEVICES];
+    int                 nb_copies;
+} b200_mirror_t;
+
 /* The device copy the runtime sees in parsec_data_t.device_copies[device_index]: a parsec_data_copy_t plus the
  * mirror inside libparsec_b200.  It stays attached for as long as the parsec_data_t lives, INVALID with
  * device_private == NULL while the tile has no HBM (the state parsec_gpu_data_reserve_device_space creates,
@@ -79,7 +89,7 @@ struct b200_module_s;
  * copies belong to their module), which is how the shim learns that the data is gone (original == NULL). */
 typedef struct b200_copy_s {
     parsec_data_copy_t    super;     /* super.super is the list item that files it in b200_module_t.copies */
-    pb2_data_t           *mirror;
+    b200_mirror_t        *mirror;
     struct b200_module_s *mod;
 } b200_copy_t;
 PARSEC_OBJ_CLASS_DECLARATION(b200_copy_t);
@@ -89,10 +99,13 @@ typedef struct b200_module_s {
     parsec_device_cuda_module_t super;
     pb2_device_t               *pb2;
     int                         pb2_index;   /* device index inside libparsec_b200 (pb2_data_state_t.owner_device) */
-    pthread_mutex_t             lock;        /* creation of mirrors, the list of copies */
-    parsec_list_t               copies;      /* every b200_copy_t of this module */
+    parsec_list_t               copies;      /* every b200_copy_t of this module (under b200_lock) */
     pb2_device_stats_t          folded;      /* what has been added to the parsec_device_module_t counters so far */
 } b200_module_t;
+
+/* creation and retirement of mirrors and copies, the modules' lists of copies: rare events, one lock for all GPUs */
+static pthread_mutex_t b200_lock = PTHREAD_MUTEX_INITIALIZER;
+static b200_module_t *b200_modules[PB2_MAX_DEVICES];   /* by pb2 device index */
 
 /* one per task in flight; pb2 frees it (free()) after the completion callback, it is the head of the block */
 typedef struct b200_task_s {
@@ -112,26 +125,28 @@ static __thread parsec_execution_stream_t *b200_tls_es = NULL;
  * ---------------------------------------------------------------------------------------------------------- */
 static int b200_pb2_to_parsec_device(const b200_module_t *mod, int pb2_owner)
 {
-    if( pb2_owner == mod->pb2_index ) return mod->super.super.super.device_index;
-    return pb2_owner <= 0 ? pb2_owner : -1;  /* 0 = host, -1 = nobody */
+    (void)mod;
+    if( pb2_owner <= 0 ) return pb2_owner;   /* 0 = host, -1 = nobody */
+    if( pb2_owner < PB2_MAX_DEVICES && NULL != b200_modules[pb2_owner] )
+        return b200_modules[pb2_owner]->super.super.super.device_index;
+    return -1;
 }
 
 /* Write the device side of the mirror into the runtime's copy. */
 static void b200_refresh_copy(b200_module_t *mod, b200_copy_t *bc, parsec_data_t *original)
 {
     pb2_data_state_t st;
-    if( PB2_SUCCESS != pb2_data_get_state(bc->mirror, mod->pb2_index, &st) ) return;
+    if( PB2_SUCCESS != pb2_data_get_state(bc->mirror->data, mod->pb2_index, &st) ) return;
     bc->super.device_private  = st.dev_ptr;
     bc->super.version         = st.dev_version;
     bc->super.coherency_state = (parsec_data_coherency_t)st.dev_coherency;
     bc->super.readers         = st.readers;
     bc->super.data_transfer_status = st.has_copy ? PARSEC_DATA_STATUS_COMPLETE_TRANSFER : PARSEC_DATA_STATUS_NOT_TRANSFER;
     if( NULL != original ) {
-        /* owner_device steers parsec_get_best_device (device.c:104-107): follow the mirror when this device takes
-         * the tile or gives it up, never touch an ownership held by somebody else */
-        const int8_t mine = (int8_t)mod->super.super.super.device_index;
+        /* owner_device steers parsec_get_best_device (device.c:104-107): the mirror knows which GPU, if any, holds the
+         * tile in write mode; a host-side owner (a CPU task wrote it) is the runtime's own business */
         int owner = b200_pb2_to_parsec_device(mod, st.owner_device);
-        if( owner == mine || original->owner_device == mine ) original->owner_device = (int8_t)owner;
+        if( owner > 1 || original->owner_device > 1 ) original->owner_device = (int8_t)owner;
     }
 }
 
@@ -139,9 +154,11 @@ static void b200_refresh_copy(b200_module_t *mod, b200_copy_t *bc, parsec_data_t
  * nothing, like a copy that reserve_device_space has just created.  Manager thread. */
 static void b200_hook_copy_released(pb2_device_t *dev, pb2_data_t *data, void *user)
 {
-    b200_copy_t *bc = (b200_copy_t*)user;
-    (void)dev; (void)data;
-    if( NULL == bc ) return;
+    b200_mirror_t *mirror = (b200_mirror_t*)user;
+    int idx = pb2_device_index(dev);
+    (void)data;
+    if( NULL == mirror || idx < 0 || idx >= PB2_MAX_DEVICES || NULL == mirror->copy[idx] ) return;
+    b200_copy_t *bc = mirror->copy[idx];
     bc->super.device_private  = NULL;
     bc->super.version         = 0;
     bc->super.coherency_state = PARSEC_DATA_COHERENCY_INVALID;
@@ -154,14 +171,14 @@ static void b200_hook_copy_released(pb2_device_t *dev, pb2_data_t *data, void *u
 
 static int b200_hook_data_alive(pb2_device_t *dev, pb2_data_t *data, void *user)
 {
-    b200_copy_t *bc = (b200_copy_t*)user;
-    (void)dev; (void)data;
-    return NULL == bc || NULL != bc->super.original;
+    b200_mirror_t *mirror = (b200_mirror_t*)user;
+    int idx = pb2_device_index(dev);
+    (void)data;
+    if( NULL == mirror || idx < 0 || idx >= PB2_MAX_DEVICES || NULL == mirror->copy[idx] ) return 1;
+    return NULL != mirror->copy[idx]->super.original;
 }
 
-static void b200_retire_copy(b200_module_t *mod, b200_copy_t *bc);
-
-/* Find or create the device copy + mirror of `original` on this device.  Any thread. */
+/* Find or create the device copy of `original` on this device, and the mirror all the GPUs share.  Any thread. */
 static b200_copy_t *b200_copy_of(b200_module_t *mod, parsec_data_t *original, parsec_data_copy_t *host, uint32_t nb_elts)
 {
     const uint8_t dev = mod->super.super.super.device_index;
@@ -170,42 +187,62 @@ static b200_copy_t *b200_copy_of(b200_module_t *mod, parsec_data_t *original, pa
         if( c->super.super.obj_class == &b200_copy_t_class ) return (b200_copy_t*)c;
         return NULL;  /* a copy attached by the user (cudaMalloc + parsec_data_copy_attach): not handled */
     }
-    pthread_mutex_lock(&mod->lock);
+    pthread_mutex_lock(&b200_lock);
     c = original->device_copies[dev];
     if( NULL == c ) {
+        b200_mirror_t *mirror = NULL;
+        for( uint32_t i = 2; i < parsec_nb_devices; i++ ) {   /* another GPU of this process already knows the tile */
+            parsec_data_copy_t *oc = original->device_copies[i];
+            if( NULL != oc && oc->super.super.obj_class == &b200_copy_t_class ) { mirror = ((b200_copy_t*)oc)->mirror; break; }
+        }
+        if( NULL == mirror ) {
+            mirror = (b200_mirror_t*)calloc(1, sizeof(b200_mirror_t));
+            mirror->data = pb2_data_create((uint64_t)original->key, NULL != original->dc ? (uint32_t)original->dc->dc_id : 0,
+                                           host->device_private, nb_elts > original->nb_elts ? nb_elts : original->nb_elts);
+            pb2_data_set_user(mirror->data, mirror);
+        }
         b200_copy_t *bc = PARSEC_OBJ_NEW(b200_copy_t);
         bc->mod = mod;
+        bc->mirror = mirror;
         bc->super.flags = PARSEC_DATA_FLAG_PARSEC_OWNED | PARSEC_DATA_FLAG_PARSEC_MANAGED;
         bc->super.coherency_state = PARSEC_DATA_COHERENCY_INVALID;
         bc->super.version = 0;
         bc->super.dtt = host->dtt;
-        bc->mirror = pb2_data_create((uint64_t)original->key, NULL != original->dc ? (uint32_t)original->dc->dc_id : 0,
-                                     host->device_private, nb_elts > original->nb_elts ? nb_elts : original->nb_elts);
-        pb2_data_set_user(bc->mirror, bc);
         if( PARSEC_SUCCESS != parsec_data_copy_attach(original, &bc->super, dev) ) {
-            pb2_data_set_user(bc->mirror, NULL);
-            pb2_data_destroy(bc->mirror);
+            if( 0 == mirror->nb_copies ) {
+                pb2_data_set_user(mirror->data, NULL);
+                pb2_data_destroy(mirror->data);
+                free(mirror);
+            }
             PARSEC_OBJ_RELEASE(bc);
-            pthread_mutex_unlock(&mod->lock);
+            pthread_mutex_unlock(&b200_lock);
             return NULL;
         }
+        mirror->copy[mod->pb2_index] = bc;
+        mirror->nb_copies++;
         parsec_list_nolock_push_back(&mod->copies, (parsec_list_item_t*)bc);
         c = &bc->super;
     }
-    pthread_mutex_unlock(&mod->lock);
+    pthread_mutex_unlock(&b200_lock);
     return c->super.super.obj_class == &b200_copy_t_class ? (b200_copy_t*)c : NULL;
 }
 
-/* Drop a copy and its mirror (the data is gone, or the module shuts down).  Only while no manager runs. */
+/* Drop a copy (the data is gone, or the module shuts down), and the mirror with its last copy.  Only while this
+ * device is idle (its manager seat is held by the caller); b200_lock held. */
 static void b200_retire_copy(b200_module_t *mod, b200_copy_t *bc)
 {
+    b200_mirror_t *mirror = bc->mirror;
     if( NULL != bc->super.original )
         parsec_data_copy_detach(bc->super.original, &bc->super, bc->super.device_index);
-    pb2_data_set_user(bc->mirror, NULL);
-    pb2_data_destroy(bc->mirror);   /* gives the HBM back */
+    mirror->copy[mod->pb2_index] = NULL;       /* the release hook finds nothing to update */
+    pb2_device_drop_copy(mod->pb2, mirror->data);   /* gives the HBM back */
+    if( 0 == --mirror->nb_copies ) {
+        pb2_data_set_user(mirror->data, NULL);
+        pb2_data_destroy(mirror->data);
+        free(mirror);
+    }
     bc->mirror = NULL;
     bc->super.device_private = NULL;
-    (void)mod;
     PARSEC_OBJ_RELEASE(bc);
 }
 
@@ -214,7 +251,7 @@ static void b200_retire_copy(b200_module_t *mod, b200_copy_t *bc)
 static void b200_collect(b200_module_t *mod, int all)
 {
     if( !pb2_device_hold(mod->pb2) ) return;
-    pthread_mutex_lock(&mod->lock);
+    pthread_mutex_lock(&b200_lock);
     parsec_list_item_t *it, *keep_head = NULL, *keep_tail = NULL;
     while( NULL != (it = parsec_list_nolock_pop_front(&mod->copies)) ) {
         b200_copy_t *bc = (b200_copy_t*)it;
@@ -232,7 +269,7 @@ static void b200_collect(b200_module_t *mod, int all)
         PARSEC_LIST_ITEM_SINGLETON(it);
         parsec_list_nolock_push_back(&mod->copies, it);
     }
-    pthread_mutex_unlock(&mod->lock);
+    pthread_mutex_unlock(&b200_lock);
     pb2_device_manage(mod->pb2);  /* nothing was queued meanwhile in the usual case: returns at once */
 }
 
@@ -241,8 +278,13 @@ static void b200_fold_stats(b200_module_t *mod)
     parsec_device_module_t *device = &mod->super.super.super;
     const pb2_device_stats_t *live = pb2_device_stats_live(mod->pb2);
     if( NULL == live ) return;
-    if( NULL != device->data_in_from_device && device->data_in_array_size > 0 )
-        device->data_in_from_device[0] += live->data_in_from_host - mod->folded.data_in_from_host;
+    if( NULL != device->data_in_from_device ) {
+        for( int i = 0; i < PB2_MAX_DEVICES; i++ ) {   /* by source: [0] = host, peers by their runtime device index */
+            uint64_t delta = live->data_in_from_device[i] - mod->folded.data_in_from_device[i];
+            int src = b200_pb2_to_parsec_device(mod, i);
+            if( 0 != delta && src >= 0 && src < (int)device->data_in_array_size ) device->data_in_from_device[src] += delta;
+        }
+    }
     device->data_out_to_host  += live->data_out_to_host  - mod->folded.data_out_to_host;
     device->required_data_in  += live->required_data_in  - mod->folded.required_data_in;
     device->required_data_out += live->required_data_out - mod->folded.required_data_out;
@@ -324,14 +366,33 @@ static void b200_complete(pb2_gpu_task_t *t, int status, void *cookie)
          * CPU copy is what the successors receive; the generated complete_hook then bumps its version */
         parsec_data_copy_t *cpu_copy = original->device_copies[0];
         if( NULL != cpu_copy ) {
-            cpu_copy->coherency_state = PARSEC_DATA_COHERENCY_SHARED;
-            cpu_copy->version = bc->super.version;
+            if( PB2_HOOK_RETURN_DONE == status ) {
+                cpu_copy->coherency_state = PARSEC_DATA_COHERENCY_SHARED;
+                cpu_copy->version = bc->super.version;
+            }
             task->data[i].data_out = cpu_copy;
         }
     }
     if( PB2_HOOK_RETURN_DONE != status ) {
-        parsec_warning("GPU[%s]: task failed on the device with status %d; no other incarnation is tried",
-                       device->name, status);
+        /* The task did not run here.  libparsec_b200 has taken its stage-in back and written the dirty inputs back to
+         * the host (parsec_cuda_kernel_cleanout's job, device_cuda_module.c:2472-2526); data_out of the written flows is
+         * the CPU copy by now.  A device that lost a CUDA call is fatal, as in the reference (:2757-2762); a body that
+         * declined sends the task to its next incarnation (:2644-2656 -- where the reference leaves chore_mask alone and
+         * would come straight back here, the CUDA incarnation is struck out first). */
+        b200_fold_stats(mod);
+        parsec_device_load[device->device_index] -= parsec_device_sweight[device->device_index];
+        free(gpu_task);
+        bt->gpu_task = NULL;
+        if( PB2_HOOK_RETURN_DISABLE == status )
+            parsec_fatal("GPU[%s]: critical issue related to the GPU discovered. Giving up", device->name);
+        for( int j = 0; NULL != task->task_class->incarnations[j].hook; j++ ) {
+            if( (task->chore_mask & (1 << j)) && PARSEC_DEV_CUDA == task->task_class->incarnations[j].type ) {
+                task->chore_mask &= ~(1 << j);
+                break;
+            }
+        }
+        __parsec_reschedule(es, task);
+        return;
     }
     device->executed_tasks++;
     b200_fold_stats(mod);
@@ -378,10 +439,10 @@ parsec_cuda_kernel_scheduler( parsec_execution_stream_t *es, parsec_gpu_task_t *
         if( NULL == host ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }
         b200_copy_t *bc = b200_copy_of(mod, original, host, gpu_task->flow_nb_elts[i]);
         if( NULL == bc ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }  /* user-managed copy: leave it to another chore */
-        pb2_data_sync_host(bc->mirror, host->device_private, host->version,
+        pb2_data_sync_host(bc->mirror->data, host->device_private, host->version,
                            PARSEC_DATA_COHERENCY_OWNED == host->coherency_state ? PB2_DATA_COHERENCY_OWNED : -1);
         bt->copy[i] = bc;
-        t->flow_data[i] = bc->mirror;
+        t->flow_data[i] = bc->mirror->data;
         t->flow_access[i] = access;           /* PARSEC_FLOW_ACCESS_* and PB2_FLOW_ACCESS_* are the same bits */
         t->flow_nb_elts[i] = gpu_task->flow_nb_elts[i];
         t->trace_dc[i] = NULL != original->dc ? (int32_t)original->dc->dc_id : 0;
@@ -531,9 +592,9 @@ static int b200_data_advise(parsec_device_module_t *device, parsec_data_t *data,
         if( NULL == host ) return PARSEC_ERR_NOT_FOUND;
         b200_copy_t *bc = b200_copy_of(mod, data, host, data->nb_elts);
         if( NULL == bc ) return PARSEC_ERR_NOT_SUPPORTED;
-        pb2_data_sync_host(bc->mirror, host->device_private, host->version,
+        pb2_data_sync_host(bc->mirror->data, host->device_private, host->version,
                            PARSEC_DATA_COHERENCY_OWNED == host->coherency_state ? PB2_DATA_COHERENCY_OWNED : -1);
-        int rc = pb2_device_data_advise(mod->pb2, bc->mirror, advice);  /* same advice values */
+        int rc = pb2_device_data_advise(mod->pb2, bc->mirror->data, advice);  /* same advice values */
         return PB2_SUCCESS == rc ? PARSEC_SUCCESS : (PB2_ERR_NOT_SUPPORTED == rc ? PARSEC_ERR_NOT_IMPLEMENTED : PARSEC_ERROR);
     }
     default:
@@ -655,14 +716,15 @@ int parsec_cuda_module_init( int dev_id, parsec_device_module_t **module )
     if( PARSEC_GPU_MAX_STREAMS != parsec_cuda_max_streams && parsec_cuda_max_streams >= 3 )
         params.max_streams = parsec_cuda_max_streams;
     params.prefetch_deferred = 1;  /* a thread that only gives advice never becomes the device's manager */
+    params.use_priorities = 1;     /* PARSEC_GPU_USE_PRIORITIES (device_gpu.h:20): task priorities order the pending list */
 
     if( PB2_SUCCESS != pb2_device_create(dev_id, &params, &mod->pb2) ) {
         free(device->name); free(mod);
         return PARSEC_ERROR;
     }
     mod->pb2_index = pb2_device_index(mod->pb2);
-    pthread_mutex_init(&mod->lock, NULL);
     PARSEC_OBJ_CONSTRUCT(&mod->copies, parsec_list_t);
+    if( mod->pb2_index >= 0 && mod->pb2_index < PB2_MAX_DEVICES ) b200_modules[mod->pb2_index] = mod;
     pb2_device_hooks_t hooks = { b200_hook_copy_released, b200_hook_data_alive };
     pb2_device_set_hooks(mod->pb2, &hooks);
 
@@ -748,6 +810,7 @@ int parsec_cuda_module_fini(parsec_device_module_t *device)
     free(gpu_device->exec_stream[0]);
     free(gpu_device->exec_stream);
     gpu_device->exec_stream = NULL;
+    if( mod->pb2_index >= 0 && mod->pb2_index < PB2_MAX_DEVICES ) b200_modules[mod->pb2_index] = NULL;
     pb2_device_destroy(mod->pb2);
     mod->pb2 = NULL;
     mod->super.cuda_index = (uint8_t)-1;
@@ -755,6 +818,5 @@ int parsec_cuda_module_fini(parsec_device_module_t *device)
     PARSEC_OBJ_DESTRUCT(&gpu_device->gpu_mem_lru);
     PARSEC_OBJ_DESTRUCT(&gpu_device->gpu_mem_owned_lru);
     PARSEC_OBJ_DESTRUCT(&mod->copies);
-    pthread_mutex_destroy(&mod->lock);
     return PARSEC_SUCCESS;
 }

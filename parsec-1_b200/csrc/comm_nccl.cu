@@ -29,11 +29,14 @@
 struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId*);
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+    ncclResult_t (*CommInitRankConfig)(ncclComm_t*, int, ncclUniqueId, int, ncclConfig_t*);  // optional
     ncclResult_t (*CommDestroy)(ncclComm_t);
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
     const char* (*GetErrorString)(ncclResult_t);
     ncclResult_t (*GroupStart)();
     ncclResult_t (*GroupEnd)();
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+    ncclResult_t (*CommAbort)(ncclComm_t);
     bool ok = false;
 };
 static NcclApi* nccl_api() {
@@ -50,12 +53,15 @@ static NcclApi* nccl_api() {
     }
     api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
     api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
+    api.CommInitRankConfig = (decltype(api.CommInitRankConfig))dlsym(h, "ncclCommInitRankConfig");
     api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
     api.Broadcast = (decltype(api.Broadcast))dlsym(h, "ncclBroadcast");
     api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
     api.GroupStart = (decltype(api.GroupStart))dlsym(h, "ncclGroupStart");
     api.GroupEnd = (decltype(api.GroupEnd))dlsym(h, "ncclGroupEnd");
-    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString &&
+    api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
+    api.CommAbort = (decltype(api.CommAbort))dlsym(h, "ncclCommAbort");
+    api.ok = api.AllReduce && api.CommAbort && api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString &&
              api.GroupStart && api.GroupEnd;
     return api.ok ? &api : nullptr;
 }
@@ -65,6 +71,7 @@ struct pb2_comm_s {
     ncclComm_t row = nullptr, col = nullptr;  // row: the Q ranks of my process row; col: the P ranks of my column
     cudaStream_t stream = nullptr;
     int cuda_index = 0;
+    int* flag = nullptr;  // one device int for pb2_comm_agree
 };
 typedef struct pb2_comm_s pb2_comm_t;
 
@@ -83,6 +90,7 @@ static void comm_free(pb2_comm_s* c) {  // whatever exists of a communicator (al
     if (c->row) nccl_api()->CommDestroy(c->row);
     if (c->col) nccl_api()->CommDestroy(c->col);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->flag) cudaFree(c->flag);
     delete c;
 }
 
@@ -100,16 +108,34 @@ extern "C" int pb2_comm_create(int cuda_index, int P, int Q, int rank, const voi
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
+    // A tile broadcast needs ~10 GB/s per GPU while the FP64 tile kernel wants every one of the 148 SMs
+    // (one CTA per SM, register bound): NCCL's default channel count took SMs away from it for no benefit (8 GPUs:
+    // kernel roofline fraction 0.951 against 0.983 on one GPU).  The communicators are therefore created with a small
+    // CTA budget; PB2_NCCL_MAX_CTAS overrides it (0 = NCCL's default).
+    int max_ctas = 2;
+    if (const char* e = getenv("PB2_NCCL_MAX_CTAS")) max_ctas = atoi(e);
+    auto init = [&](ncclComm_t* comm, int n, const ncclUniqueId& id, int me) {
+        if (max_ctas > 0 && nccl->CommInitRankConfig) {
+            ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+            cfg.minCTAs = 1;
+            cfg.maxCTAs = max_ctas;
+            if (nccl->CommInitRankConfig(comm, n, id, me, &cfg) == ncclSuccess) return true;
+            *comm = nullptr;
+            return false;
+        }
+        return nccl->CommInitRank(comm, n, id, me) == ncclSuccess;
+    };
+    if (cudaMalloc((void**)&c->flag, sizeof(int)) != cudaSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
     ncclUniqueId rid, cid;
     if (Q > 1) {
         if (!row_id) { comm_free(c); return PB2_ERR_BAD_PARAM; }
         memcpy(&rid, row_id, 128);
-        if (nccl->CommInitRank(&c->row, Q, rid, c->mycol) != ncclSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
+        if (!init(&c->row, Q, rid, c->mycol)) { comm_free(c); return PB2_ERR_DEVICE; }
     }
     if (P > 1) {
         if (!col_id) { comm_free(c); return PB2_ERR_BAD_PARAM; }
         memcpy(&cid, col_id, 128);
-        if (nccl->CommInitRank(&c->col, P, cid, c->myrow) != ncclSuccess) { comm_free(c); return PB2_ERR_DEVICE; }
+        if (!init(&c->col, P, cid, c->myrow)) { comm_free(c); return PB2_ERR_DEVICE; }
     }
     *out = c;
     return PB2_SUCCESS;
@@ -130,6 +156,30 @@ extern "C" int pb2_comm_group_begin(pb2_comm_t* c) {
 }
 extern "C" int pb2_comm_group_end(pb2_comm_t* c) {
     return (c && nccl_api() && nccl_api()->GroupEnd() == ncclSuccess) ? PB2_SUCCESS : PB2_ERR_DEVICE;
+}
+
+// Every rank of the grid says whether it can go ahead (ok != 0); returns 1 only if all of them can.  Two tiny
+// all-reduces (MIN), along the process row and then along the process column, reach the whole P x Q grid.  Used before
+// a taskpool issues its first broadcast: a rank that cannot take part (its HBM heap cannot hold the operands of one
+// lookahead window, say) must not leave the others blocked inside a collective.
+extern "C" int pb2_comm_agree(pb2_comm_t* c, int ok) {
+    if (!c || !c->flag) return 0;
+    int v = ok ? 1 : 0;
+    if (cudaMemcpyAsync(c->flag, &v, sizeof(int), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) return 0;
+    for (ncclComm_t comm : {c->row, c->col})
+        if (comm && nccl_api()->AllReduce(c->flag, c->flag, 1, ncclInt, ncclMin, comm, c->stream) != ncclSuccess) return 0;
+    if (cudaMemcpyAsync(&v, c->flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) return 0;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) return 0;
+    return v;
+}
+
+// A rank that has to leave the collective sequence half-way (a CUDA or allocation failure after pb2_comm_agree) aborts
+// both communicators: its peers then get an error out of NCCL instead of waiting for ever.
+extern "C" int pb2_comm_abort(pb2_comm_t* c) {
+    if (!c) return PB2_ERR_BAD_PARAM;
+    if (c->row) { nccl_api()->CommAbort(c->row); c->row = nullptr; }
+    if (c->col) { nccl_api()->CommAbort(c->col); c->col = nullptr; }
+    return PB2_SUCCESS;
 }
 
 extern "C" void* pb2_comm_stream(pb2_comm_t* c) { return c ? (void*)c->stream : nullptr; }

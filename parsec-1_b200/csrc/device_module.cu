@@ -25,6 +25,7 @@
 #include <algorithm>
 #include <chrono>
 #include <thread>
+#include <unordered_set>
 
 #include "pb2_internal.h"
 #include "pb2_types.h"
@@ -48,7 +49,18 @@ struct TaskState {  // module-private part of a task in flight (pb2_gpu_task_t.r
     int exec_stream = -1;
     bool is_w2r = false;
     std::vector<pb2_copy_t*> w2r_copies;
-    uint32_t pushed_mask = 0;  // flows for which THIS task scheduled the H2D
+    uint32_t pushed_mask = 0;  // flows for which THIS task scheduled the copy in (H2D, or D2D from a peer GPU)
+    uint32_t staged_mask = 0;  // flows whose stage-in bookkeeping has been applied (what a cleanout has to undo)
+    // state of each staged flow's device copy before this task touched it, for parsec_cuda_kernel_cleanout's job
+    struct Before {
+        uint32_t version;
+        uint8_t coherency, host_coherency, list_id;
+        int8_t owner;
+    } before[PB2_MAX_PARAM_COUNT];
+    // peer-GPU copies this task reads from (D2D stage-in): pinned (readers++) until the task retires
+    pb2_copy_t* d2d_src[PB2_MAX_PARAM_COUNT] = {nullptr};
+    uint8_t d2d_demote[PB2_MAX_PARAM_COUNT] = {0};  // the source gave its ownership away: invalidate it when unpinned
+    bool host_source_only = false;  // no D2D source (a pin that outlives this record could not hand the reader back)
 };
 
 struct InFlight {
@@ -66,15 +78,34 @@ struct pb2_device_s {
     pb2_device_params_t params;
     std::atomic<int32_t> mutex{0};  // tasks inside the module (parsec_device_gpu_module_t.mutex)
     std::mutex pending_lock;
-    std::deque<pb2_gpu_task_t*> pending;  // parsec_device_gpu_module_t.pending
+    // parsec_device_gpu_module_t.pending.  A binary heap: highest task priority first, oldest first among equals
+    // (the reference keeps its per-stream lists priority-ordered, PARSEC_GPU_USE_PRIORITIES, device_cuda_module.c:1683-1692);
+    // with params.use_priorities == 0 every entry has priority 0 and the heap is a FIFO.
+    struct Pending {
+        pb2_gpu_task_t* task;
+        int32_t priority;
+        uint64_t seq;
+        bool operator<(const Pending& o) const { return priority != o.priority ? priority < o.priority : seq > o.seq; }
+    };
+    std::vector<Pending> pending;
+    uint64_t pending_seq = 0;
     std::deque<pb2_gpu_task_t*> deferred; // prefetches queued while nobody managed the device (not counted in mutex)
+    // copies of THIS device that a peer GPU's task has finished reading (D2D stage-in): the peer's manager must not
+    // touch this device's lists, so it leaves the copy here; this device's manager (or memory_release / destroy)
+    // drops the reader and re-files the copy.  The job of the reference's D2D_COMPLETE command task (:1733-1760).
+    struct PeerUnpin {
+        pb2_copy_t* copy;
+        bool demote;
+    };
+    std::mutex peer_lock;
+    std::vector<PeerUnpin> peer_unpins;
     // everything below is touched by the manager only
     cudaStream_t h2d = nullptr, d2h = nullptr;
     std::vector<cudaStream_t> exec;
     std::vector<uint64_t> exec_waited_seq;
     int next_exec = 0;
     int active_exec = 0;  // exec streams the last task was spread over (see try_submit)
-    uint64_t h2d_seq = 0;  // number of push events recorded so far
+    std::atomic<uint64_t> h2d_seq{0};  // number of push events recorded so far (a peer GPU reads it to wait for a source copy)
     cudaEvent_t h2d_events[pb2::EVENT_RING] = {};
     std::vector<cudaEvent_t> event_pool;
     // in flight, one FIFO per stream that carries the final event: exec streams, then d2h, then h2d (prefetches).
@@ -89,6 +120,7 @@ struct pb2_device_s {
     pb2_device_stats_t stats;
     std::vector<pb2_event_t> events;
     bool failed = false;
+    uint32_t peer_access_mask = 0;  // bit i: CUDA device i is directly reachable (parsec_device_gpu_module_t.peer_access_mask)
     struct Workspace {  // parsec_gpu_workspace_t (device_gpu.h:155-159), one per exec stream
         void* buf[PB2_GPU_MAX_WORKSPACE] = {nullptr};
         int stack_head = -1;
@@ -98,6 +130,7 @@ struct pb2_device_s {
     std::vector<Workspace> workspace;
     std::unordered_map<void*, size_t> registered;
     pb2_device_hooks_t hooks = {nullptr, nullptr};
+    std::unordered_set<pb2_copy_t*> all_copies;  // every device copy this module has created and not released yet
     std::vector<std::vector<cudaEvent_t>> launch_marks;  // profile_launches: completion marks per exec stream
 };
 
@@ -105,6 +138,9 @@ static std::mutex g_devices_lock;
 static pb2_device_s* g_devices[PB2_MAX_DEVICES] = {nullptr};
 
 using namespace pb2;
+
+static void drain_peer_unpins(pb2_device_s* d);
+static void complete_w2r(pb2_device_s* d, TaskState* st);
 
 extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->memory_use_percent = 95;
@@ -117,6 +153,7 @@ extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->profile_launches = 0;
     p->sort_pending_tasks = 0;
     p->prefetch_deferred = 0;
+    p->use_priorities = 0;
 }
 
 // The reference's MCA parameters reach a process as environment variables PARSEC_MCA_<name> (parsec/utils/mca_param.c;
@@ -262,12 +299,35 @@ extern "C" int pb2_device_create(int cuda_index, const pb2_device_params_t* para
     }
     d->heap = new ZoneHeap(d->hbm_base, (int)nblocks, unit);
     d->stats.hbm_bytes_total = nblocks * unit;
+    // direct access between the GPUs of this process, both ways (device_cuda_component.c:120-151): a tile that sits on
+    // a peer is staged over NVLink instead of PCIe.  Without it cudaMemcpyPeerAsync still works, through host memory.
+    {
+        std::lock_guard<std::mutex> g(g_devices_lock);
+        for (int i = 2; i < PB2_MAX_DEVICES; ++i) {
+            pb2_device_s* o = g_devices[i];
+            if (!o || o == d || o->cuda_index == d->cuda_index) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, d->cuda_index, o->cuda_index) == cudaSuccess && can) {
+                cudaSetDevice(d->cuda_index);
+                if (cudaDeviceEnablePeerAccess(o->cuda_index, 0) != cudaSuccess) cudaGetLastError();
+                d->peer_access_mask |= 1u << o->cuda_index;
+            }
+            can = 0;
+            if (cudaDeviceCanAccessPeer(&can, o->cuda_index, d->cuda_index) == cudaSuccess && can) {
+                cudaSetDevice(o->cuda_index);
+                if (cudaDeviceEnablePeerAccess(d->cuda_index, 0) != cudaSuccess) cudaGetLastError();
+                o->peer_access_mask |= 1u << d->cuda_index;
+            }
+        }
+        cudaSetDevice(d->cuda_index);
+    }
     *out = d;
     return PB2_SUCCESS;
 }
 
 static void release_copy(pb2_device_s* d, pb2_copy_t* c) {  // detach + give the memory back
     CopyList::chop(c, d->lists);
+    d->all_copies.erase(c);
     pb2_data_s* original = c->original;
     if (original) original->device_copies[d->device_index] = nullptr;
     if ((c->flags & PB2_FLAG_OWNED) && c->device_private) d->heap->free(c->device_private);
@@ -297,6 +357,7 @@ extern "C" int pb2_device_stream_index(const pb2_device_t* d, const void* cuda_s
 extern "C" int pb2_device_memory_release(pb2_device_t* d) {
     if (!d) return PB2_ERR_BAD_PARAM;
     if (d->mutex.load() != 0) return PB2_ERROR;  // a manager is active
+    drain_peer_unpins(d);
     std::vector<pb2_copy_t*> busy;
     while (pb2_copy_t* c = d->lru.pop_front()) {
         if (c->readers != 0) {  // pinned by a reader (e.g. the comm layer): keep it
@@ -313,8 +374,16 @@ extern "C" int pb2_device_destroy(pb2_device_t* d) {
     if (!d) return PB2_ERR_BAD_PARAM;
     cudaSetDevice(d->cuda_index);
     cudaDeviceSynchronize();
-    while (pb2_copy_t* c = d->lru.pop_front()) release_copy(d, c);
-    while (pb2_copy_t* c = d->owned_lru.pop_front()) release_copy(d, c);
+    // whatever is still queued is abandoned: write-backs have completed (the device is idle), tasks never ran
+    for (auto& queue : d->inflight_q)
+        for (auto& f : queue) {
+            if (f.st && f.st->is_w2r) complete_w2r(d, f.st);
+            delete f.st;
+        }
+    for (pb2_gpu_task_t* t : d->deferred) free(t);
+    drain_peer_unpins(d);
+    // every copy, also the ones in no list (dropped from the LRU while they had readers, or chopped out for a writer)
+    while (!d->all_copies.empty()) release_copy(d, *d->all_copies.begin());
     pb2_device_free_workspace(d);
     for (auto& kv : d->registered) cudaHostUnregister(kv.first);
     for (cudaStream_t s : d->exec)
@@ -446,6 +515,45 @@ extern "C" int pb2_default_stage_out(pb2_gpu_task_t* t, uint32_t flow_mask, void
 }
 
 // ------------------------------------------------------------------------------------ reserve (a4)
+// A CUDA call failed on the manager thread: the device is unusable from here on (the reference returns
+// PARSEC_HOOK_RETURN_DISABLE and gives up, device_cuda_module.c:2757-2762).
+#define PB2_DEV_TRY(d, call)                                                                                      \
+    do {                                                                                                          \
+        cudaError_t e__ = (call);                                                                                 \
+        if (e__ != cudaSuccess) {                                                                                 \
+            fprintf(stderr, "[parsec_b200] CUDA error %s at %s:%d (%s)\n", cudaGetErrorString(e__), __FILE__,     \
+                    __LINE__, #call);                                                                             \
+            (d)->failed = true;                                                                                   \
+            return PB2_HOOK_RETURN_DISABLE;                                                                       \
+        }                                                                                                         \
+    } while (0)
+
+// Readers that a peer GPU's manager has handed back (see pb2_device_s::peer_unpins).  Manager thread, or any thread
+// while no manager runs.
+static void drain_peer_unpins(pb2_device_s* d) {
+    std::vector<pb2_device_s::PeerUnpin> todo;
+    {
+        std::lock_guard<std::mutex> g(d->peer_lock);
+        todo.swap(d->peer_unpins);
+    }
+    for (const auto& u : todo) {
+        pb2_copy_t* c = u.copy;
+        pb2_data_s* original = c->original;
+        std::unique_lock<std::mutex> lk;
+        if (original) lk = std::unique_lock<std::mutex>(original->lock);
+        c->readers--;
+        if (u.demote) {  // a peer took the tile over in write mode: what is left here is about to be outdated
+            c->coherency_state = PB2_DATA_COHERENCY_INVALID;
+            if (c->readers == 0) {
+                CopyList::chop(c, d->lists);
+                d->lru.push_front(c);  // first candidate for eviction
+            }
+        } else if (c->readers == 0 && c->list_id == 0 && c->coherency_state != PB2_DATA_COHERENCY_OWNED) {
+            d->lru.push_back(c);
+        }
+    }
+}
+
 // Returns 0 = every flow has a device copy, 1 = no room right now, 2 = a needed copy is being written back.
 // zone_malloc with eviction from the clean LRU (:934-1113).  `t` (may be null) is the task being served: its own
 // tiles are never stolen (:1041-1062).  Returns nullptr when nothing evictable is left.
@@ -455,7 +563,6 @@ static void* alloc_evicting(pb2_device_s* d, size_t bytes, pb2_gpu_task_t* t) {
         pb2_copy_t* victim = nullptr;
         std::vector<pb2_copy_t*> skipped;
         while (pb2_copy_t* cand = d->lru.pop_front()) {
-            if (cand->readers != 0) continue;  // dropped from the list; pop re-files it when readers hit 0
             bool mine = false;
             if (t)
                 for (int j = 0; j < t->nb_flows; ++j)
@@ -464,6 +571,12 @@ static void* alloc_evicting(pb2_device_s* d, size_t bytes, pb2_gpu_task_t* t) {
                 skipped.push_back(cand);
                 continue;
             }
+            // readers are checked, and the copy detached, under the tile's lock: a peer GPU that wants this copy as
+            // the source of a D2D stage-in pins it under the same lock, so it either sees the copy pinned or not at all
+            std::unique_lock<std::mutex> lk;
+            if (cand->original) lk = std::unique_lock<std::mutex>(cand->original->lock);
+            if (cand->readers != 0) continue;  // dropped from the list; whoever takes the last reader away re-files it
+            if (cand->original) cand->original->device_copies[d->device_index] = nullptr;
             victim = cand;
             break;
         }
@@ -494,14 +607,16 @@ static int reserve_device_space(pb2_device_s* d, pb2_gpu_task_t* t) {
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(t->flow_access[i] & PB2_FLOW_ACCESS_RW) || !t->flow_data[i]) continue;
         pb2_data_s* master = t->flow_data[i];
-        std::lock_guard<std::mutex> g(master->lock);
-        pb2_copy_t* c = master->device_copies[d->device_index];
-        if (c) {
-            if (c->data_transfer_status == PB2_XFER_UNDER) {
-                // only a W2R write-back leaves a copy UNDER_TRANSFER here (pushes are booked eagerly)
-                return 2;
+        {
+            std::lock_guard<std::mutex> g(master->lock);
+            pb2_copy_t* c = master->device_copies[d->device_index];
+            if (c) {
+                if (c->data_transfer_status == PB2_XFER_UNDER) {
+                    // only a W2R write-back leaves a copy UNDER_TRANSFER here (pushes are booked eagerly)
+                    return 2;
+                }
+                continue;
             }
-            continue;
         }
         void* mem = alloc_evicting(d, t->flow_nb_elts[i], t);
         if (!mem) {
@@ -513,15 +628,19 @@ static int reserve_device_space(pb2_device_s* d, pb2_gpu_task_t* t) {
                 }
             return 1;
         }
-        c = new pb2_copy_t();
+        pb2_copy_t* c = new pb2_copy_t();
         c->flags = PB2_FLAG_OWNED | PB2_FLAG_MANAGED;
         c->device_private = mem;
         c->coherency_state = PB2_DATA_COHERENCY_INVALID;
         c->version = 0;
         c->device_index = (int8_t)d->device_index;
         c->original = master;
-        master->device_copies[d->device_index] = c;
+        {
+            std::lock_guard<std::mutex> g(master->lock);
+            master->device_copies[d->device_index] = c;
+        }
         d->lru.push_back(c);
+        d->all_copies.insert(c);
         fresh[i] = c;
         trace(d, t, i, EV_RESERVE, 0);
     }
@@ -529,6 +648,35 @@ static int reserve_device_space(pb2_device_s* d, pb2_gpu_task_t* t) {
 }
 
 // ------------------------------------------------------------------------------------ stage-in (a5, a6)
+// Where the bytes come from (parsec_gpu_data_stage_in, :1260-1530).  `from` is what the ownership state machine
+// answered: -1 = nothing to move, 0 = the host copy, >= 2 = the device that holds the valid copy.  A read-only flow
+// whose tile also sits, at the version wanted, on another GPU of this process is taken from there rather than from
+// the host (:1310-1378: NVLink instead of PCIe); a tile whose only valid copy is on another GPU has no other source.
+// The source copy is pinned (readers++) under the tile's lock, which the caller holds.
+static pb2_copy_t* pick_peer_source(pb2_device_s* d, pb2_data_s* original, int from, uint8_t type, pb2_device_s** src_dev) {
+    *src_dev = nullptr;
+    if (from >= 2 && from != d->device_index) {
+        pb2_copy_t* c = original->device_copies[from];
+        pb2_device_s* sd = g_devices[from];
+        if (c && sd && c->coherency_state != PB2_DATA_COHERENCY_INVALID) {
+            *src_dev = sd;
+            return c;
+        }
+        return nullptr;
+    }
+    if (from == 0 && !(type & PB2_FLOW_ACCESS_WRITE)) {
+        for (int p = 2; p < PB2_MAX_DEVICES; ++p) {
+            pb2_copy_t* c = original->device_copies[p];
+            if (p == d->device_index || !c || !g_devices[p]) continue;
+            if (c->coherency_state == PB2_DATA_COHERENCY_INVALID || c->version != original->host_copy.version) continue;
+            if (c->data_transfer_status != PB2_XFER_COMPLETE) continue;  // e.g. being written back: take the host copy
+            *src_dev = g_devices[p];
+            return c;
+        }
+    }
+    return nullptr;
+}
+
 static int stage_in_flow(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int i, bool* issued) {
     pb2_data_s* original = t->flow_data[i];
     const uint8_t type = t->flow_access[i];
@@ -538,15 +686,19 @@ static int stage_in_flow(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int 
     t->flow_dev_ptr[i] = gpu->device_private;
     t->flow_host_ptr[i] = in->device_private;
 
-    if (type & PB2_FLOW_ACCESS_WRITE) {
-        if (gpu->readers > 0 && !(gpu->readers == 1 && (type & PB2_FLOW_ACCESS_READ))) {
-            fprintf(stderr, "[parsec_b200] write access to a tile with %d readers (missing CTL dependency)\n",
-                    gpu->readers);
-            return -1;
-        }
-        CopyList::chop(gpu, d->lists);  // written tiles leave the LRU lists until the task completes
+    if ((type & PB2_FLOW_ACCESS_WRITE) && gpu->readers > 0 && !(gpu->readers == 1 && (type & PB2_FLOW_ACCESS_READ))) {
+        fprintf(stderr, "[parsec_b200] write access to a tile with %d readers (missing CTL dependency)\n", gpu->readers);
+        return PB2_HOOK_RETURN_ERROR;
     }
+    TaskState::Before& b = st->before[i];
+    b.version = gpu->version;
+    b.coherency = gpu->coherency_state;
+    b.host_coherency = in->coherency_state;
+    b.list_id = (uint8_t)gpu->list_id;
+    b.owner = original->owner_device;
+    if (type & PB2_FLOW_ACCESS_WRITE) CopyList::chop(gpu, d->lists);  // written tiles leave the LRU lists until the task completes
     int from = data_start_transfer_ownership(original, d->device_index, type);
+    st->staged_mask |= 1u << i;
     if ((type & PB2_FLOW_ACCESS_WRITE) && t->task_type != 1) gpu->version++;
     if (from == -1) {
         gpu->data_transfer_status = PB2_XFER_COMPLETE;
@@ -555,13 +707,43 @@ static int stage_in_flow(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int 
         return 0;
     }
     d->stats.required_data_in += original->nb_elts;
-    pb2_stage_fn fn = t->stage_in ? t->stage_in : pb2_default_stage_in;
-    if (fn(t, 1u << i, d->h2d) != PB2_SUCCESS) return -1;
-    d->stats.data_in_from_host += t->flow_nb_elts[i];
+    pb2_device_s* src_dev = nullptr;
+    pb2_copy_t* src = (t->stage_in || st->host_source_only) ? nullptr : pick_peer_source(d, original, from, type, &src_dev);
+    if (from >= 2 && from != d->device_index && !src) {
+        fprintf(stderr, "[parsec_b200] the valid copy of a tile is on device %d, which cannot serve it\n", from);
+        return PB2_HOOK_RETURN_ERROR;
+    }
+    if (src) {
+        // the source's bytes are valid once its own device's stage-in (or the broadcast that delivered it) is done
+        const uint64_t sseq = src->ready_seq, snow = src_dev->h2d_seq.load();
+        if (sseq) {
+            const uint64_t w = (snow - sseq >= (uint64_t)EVENT_RING) ? snow : sseq;
+            PB2_DEV_TRY(d, cudaStreamWaitEvent(d->h2d, src_dev->h2d_events[w % EVENT_RING], 0));
+        }
+        if (src->ready_event) PB2_DEV_TRY(d, cudaStreamWaitEvent(d->h2d, src->ready_event, 0));
+        PB2_DEV_TRY(d, cudaMemcpyPeerAsync(gpu->device_private, d->cuda_index, src->device_private, src_dev->cuda_index,
+                                           t->flow_nb_elts[i], d->h2d));
+        src->readers++;
+        st->d2d_src[i] = src;
+        // a writer takes the tile away from the peer: its copy is outdated as soon as this task has run
+        st->d2d_demote[i] = (type & PB2_FLOW_ACCESS_WRITE) ? 1 : 0;
+        // the version stays the host copy's, as when the reference stages from task->data[i].data_in (:1498): after a
+        // completed writer the host copy carries version + 1 for bytes that only the owner GPU has
+        d->stats.data_in_from_peers += t->flow_nb_elts[i];
+        d->stats.data_in_from_device[src_dev->device_index] += t->flow_nb_elts[i];
+    } else {
+        pb2_stage_fn fn = t->stage_in ? t->stage_in : pb2_default_stage_in;
+        if (fn(t, 1u << i, d->h2d) != PB2_SUCCESS) {
+            d->failed = true;
+            return PB2_HOOK_RETURN_DISABLE;
+        }
+        d->stats.data_in_from_host += t->flow_nb_elts[i];
+        d->stats.data_in_from_device[0] += t->flow_nb_elts[i];
+    }
     if (t->task_type == 0) d->stats.nb_data_faults += t->flow_nb_elts[i];
     gpu->version = in->version;
     gpu->data_transfer_status = PB2_XFER_UNDER;
-    gpu->ready_seq = d->h2d_seq + 1;  // the push event recorded right after this task's copies
+    gpu->ready_seq = d->h2d_seq.load() + 1;  // the push event recorded right after this task's copies
     st->pushed_mask |= 1u << i;
     *issued = true;
     trace(d, t, i, EV_STAGE_IN, 1);
@@ -576,6 +758,70 @@ static void complete_push_flow(pb2_device_s* d, pb2_gpu_task_t* t, int i) {
     gpu->data_transfer_status = PB2_XFER_COMPLETE;
     data_end_transfer_ownership(original, d->device_index, t->flow_access[i]);
     trace(d, t, i, EV_PUSH_DONE, 0);
+}
+
+// hand the readers of D2D sources back to the devices that own those copies
+static void release_peer_sources(pb2_device_s* d, TaskState* st, int nb_flows) {
+    (void)d;
+    for (int i = 0; i < nb_flows; ++i) {
+        pb2_copy_t* src = st->d2d_src[i];
+        if (!src) continue;
+        st->d2d_src[i] = nullptr;
+        pb2_device_s* sd = g_devices[src->device_index];
+        if (!sd) continue;
+        std::lock_guard<std::mutex> g(sd->peer_lock);
+        sd->peer_unpins.push_back({src, st->d2d_demote[i] != 0});
+    }
+}
+
+// ------------------------------------------------------------------------------------ cleanout (a10)
+// parsec_cuda_kernel_cleanout (:2472-2526): the task will not run on this device after all (its body declined, or a
+// flow could not be staged).  Everything stage-in did to the task's tiles is taken back: readers, the version bump
+// of WRITE flows, coherency and ownership, the LRU list each copy sat in.  A flow whose bytes were already requested
+// from the host keeps them: the copy is then a clean SHARED copy of the host version.  Dirty inputs (the previous
+// links of a C chain) are written back first, synchronously: the next incarnation of the task reads host memory,
+// and unlike the reference this module does not leave it stale.
+static void cleanout_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
+    bool wrote_back = false;
+    for (int i = 0; i < t->nb_flows; ++i) {
+        if (!(st->staged_mask & (1u << i))) continue;
+        pb2_data_s* original = t->flow_data[i];
+        const uint8_t type = t->flow_access[i];
+        std::lock_guard<std::mutex> g(original->lock);
+        pb2_copy_t* gpu = original->device_copies[d->device_index];
+        pb2_copy_t* cpu = &original->host_copy;
+        const TaskState::Before& b = st->before[i];
+        if (type & PB2_FLOW_ACCESS_READ) gpu->readers--;
+        original->owner_device = b.owner;
+        cpu->coherency_state = b.host_coherency;
+        CopyList::chop(gpu, d->lists);
+        if (st->pushed_mask & (1u << i)) {  // the copy in is already queued: keep the bytes, as a clean copy
+            gpu->coherency_state = PB2_DATA_COHERENCY_SHARED;
+            gpu->data_transfer_status = PB2_XFER_COMPLETE;
+            if (gpu->readers == 0) d->lru.push_back(gpu);
+            continue;
+        }
+        gpu->version = b.version;
+        gpu->coherency_state = b.coherency;
+        if (b.list_id == 2 && gpu->readers == 0) {
+            // dirty: newer than the host copy.  Bring the host up to date so that another incarnation can read it.
+            if (copy_tile(original, gpu->device_private, cpu->device_private, original->nb_elts, false, d->d2h) == cudaSuccess) {
+                wrote_back = true;
+                d->stats.data_out_to_host += original->nb_elts;
+                gpu->coherency_state = PB2_DATA_COHERENCY_SHARED;
+                cpu->coherency_state = PB2_DATA_COHERENCY_SHARED;
+                d->lru.push_back(gpu);
+            } else {
+                d->failed = true;
+                d->owned_lru.push_back(gpu);
+            }
+        } else if (gpu->readers == 0) {
+            (b.list_id == 2 ? d->owned_lru : d->lru).push_back(gpu);
+        }
+    }
+    release_peer_sources(d, st, t->nb_flows);
+    if (wrote_back && cudaStreamSynchronize(d->d2h) != cudaSuccess) d->failed = true;
+    d->stats.nb_cleanouts++;
 }
 
 // ------------------------------------------------------------------------------------ W2R (a11)
@@ -595,10 +841,13 @@ static bool start_w2r(pb2_device_s* d) {
             continue;
         }
         if (c->readers == 0) {
-            CopyList::chop(c, d->lists);
-            c->readers++;
-            c->data_transfer_status = PB2_XFER_UNDER;
-            st->w2r_copies.push_back(c);
+            std::lock_guard<std::mutex> lk(c->original->lock);
+            if (c->readers == 0) {
+                CopyList::chop(c, d->lists);
+                c->readers++;
+                c->data_transfer_status = PB2_XFER_UNDER;
+                st->w2r_copies.push_back(c);
+            }
         }
         c = next;
     }
@@ -607,12 +856,18 @@ static bool start_w2r(pb2_device_s* d) {
         return false;
     }
     // the dirty bytes were produced on exec streams whose completion the host has already observed
+    bool ok = true;
     for (pb2_copy_t* c : st->w2r_copies) {
-        copy_tile(c->original, c->device_private, c->original->host_copy.device_private, c->original->nb_elts, false, d->d2h);
+        ok = ok && copy_tile(c->original, c->device_private, c->original->host_copy.device_private, c->original->nb_elts,
+                             false, d->d2h) == cudaSuccess;
         d->stats.data_out_to_host += c->original->nb_elts;
     }
     st->done = get_event(d);
-    cudaEventRecord(st->done, d->d2h);
+    ok = ok && st->done && cudaEventRecord(st->done, d->d2h) == cudaSuccess;
+    if (!ok) {
+        fprintf(stderr, "[parsec_b200] CUDA error while writing dirty tiles back: %s\n", cudaGetErrorString(cudaGetLastError()));
+        d->failed = true;
+    }
     d->inflight_q[d->exec.size()].push_back({nullptr, st});
     d->inflight_count++;
     d->stats.nb_w2r_tasks++;
@@ -658,25 +913,26 @@ static void complete_w2r(pb2_device_s* d, TaskState* st) {
 }
 
 // ------------------------------------------------------------------------------------ submit one task
-// 0 = in flight, 1 = stalled (no room / write-back pending), <0 = error
-static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
-    int r = reserve_device_space(d, t);
-    if (r != 0) return 1;
-    TaskState* st = new TaskState();
-    t->reserved[0] = st;
+// 0 = in flight, 1 = stalled (no room / write-back pending); negative = the task does not run here:
+// PB2_HOOK_RETURN_DISABLE when a CUDA call failed (the device is unusable), any other negative value is the task's own
+// (its body declined or a flow could not be staged) and leaves the device healthy.  In every negative case what
+// stage-in did has been taken back (cleanout_task) and t->reserved[0] is clear.
+static int try_submit_inner(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     bool issued = false;
     uint64_t need_seq = 0;
     std::vector<cudaEvent_t> extra_waits;
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(t->flow_access[i] & PB2_FLOW_ACCESS_RW) || !t->flow_data[i]) continue;
-        if (stage_in_flow(d, t, st, i, &issued) < 0) return PB2_HOOK_RETURN_ERROR;
+        int rc = stage_in_flow(d, t, st, i, &issued);
+        if (rc < 0) return rc;
         pb2_copy_t* c = t->flow_data[i]->device_copies[d->device_index];
         need_seq = std::max(need_seq, c->ready_seq);
         if (c->ready_event) extra_waits.push_back(c->ready_event);
     }
     if (issued) {
-        d->h2d_seq++;
-        cudaEventRecord(d->h2d_events[d->h2d_seq % EVENT_RING], d->h2d);
+        const uint64_t seq = d->h2d_seq.load() + 1;
+        PB2_DEV_TRY(d, cudaEventRecord(d->h2d_events[seq % EVENT_RING], d->h2d));
+        d->h2d_seq.store(seq);
     }
     for (int i = 0; i < t->nb_flows; ++i)
         if (st->pushed_mask & (1u << i)) complete_push_flow(d, t, i);
@@ -698,19 +954,19 @@ static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
         if (need_seq > d->exec_waited_seq[s]) {
             // waiting on a newer event of the same in-order stream covers every older one; if the ring has
             // wrapped past need_seq the slot holds a later event, which is still sufficient
-            uint64_t w = (d->h2d_seq - need_seq >= (uint64_t)EVENT_RING) ? d->h2d_seq : need_seq;
-            cudaStreamWaitEvent(d->exec[s], d->h2d_events[w % EVENT_RING], 0);
+            const uint64_t now = d->h2d_seq.load();
+            uint64_t w = (now - need_seq >= (uint64_t)EVENT_RING) ? now : need_seq;
+            PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], d->h2d_events[w % EVENT_RING], 0));
             d->exec_waited_seq[s] = w;
         }
-        for (cudaEvent_t e : extra_waits) cudaStreamWaitEvent(d->exec[s], e, 0);
+        for (cudaEvent_t e : extra_waits) PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], e, 0));
         int rc = t->submit(d, t, d->exec[s]);
-        if (rc != PB2_HOOK_RETURN_DONE) return rc < 0 ? rc : PB2_HOOK_RETURN_ERROR;
+        if (rc != PB2_HOOK_RETURN_DONE) return rc < 0 && rc != PB2_HOOK_RETURN_DISABLE ? rc : PB2_HOOK_RETURN_ERROR;
         d->stats.kernel_launches++;
         if (d->params.profile_launches && d->launch_marks[s].size() < 16384) {
             cudaEvent_t mark = nullptr;
-            cudaEventCreate(&mark);
-            cudaEventRecord(mark, d->exec[s]);
-            d->launch_marks[s].push_back(mark);
+            if (cudaEventCreate(&mark) == cudaSuccess && cudaEventRecord(mark, d->exec[s]) == cudaSuccess)
+                d->launch_marks[s].push_back(mark);
         }
         last = d->exec[s];
     }
@@ -719,14 +975,21 @@ static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
     for (int i = 0; i < t->nb_flows; ++i)
         if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && (t->pushout & (1 << i))) out_mask |= 1u << i;
     st->done = get_event(d);
+    if (!st->done) {
+        d->failed = true;
+        return PB2_HOOK_RETURN_DISABLE;
+    }
     if (out_mask) {
-        cudaEventRecord(st->done, last);
-        cudaStreamWaitEvent(d->d2h, st->done, 0);
+        PB2_DEV_TRY(d, cudaEventRecord(st->done, last));
+        PB2_DEV_TRY(d, cudaStreamWaitEvent(d->d2h, st->done, 0));
         pb2_stage_fn fn = t->stage_out ? t->stage_out : pb2_default_stage_out;
-        if (fn(t, out_mask, d->d2h) != PB2_SUCCESS) return PB2_HOOK_RETURN_ERROR;
-        cudaEventRecord(st->done, d->d2h);
+        if (fn(t, out_mask, d->d2h) != PB2_SUCCESS) {
+            d->failed = true;
+            return PB2_HOOK_RETURN_DISABLE;
+        }
+        PB2_DEV_TRY(d, cudaEventRecord(st->done, d->d2h));
     } else {
-        cudaEventRecord(st->done, last);
+        PB2_DEV_TRY(d, cudaEventRecord(st->done, last));
     }
     const size_t q = out_mask ? d->exec.size() : (st->exec_stream >= 0 ? (size_t)st->exec_stream : d->exec.size() + 1);
     d->inflight_q[q].push_back({t, st});
@@ -734,8 +997,25 @@ static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
     return 0;
 }
 
+static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
+    int r = reserve_device_space(d, t);
+    if (r != 0) return 1;
+    TaskState* st = new TaskState();
+    t->reserved[0] = st;
+    int rc = try_submit_inner(d, t, st);
+    if (rc < 0) {
+        // if the body was already launched the kernel may be running: let the streams drain before the tiles go back
+        if (rc == PB2_HOOK_RETURN_DISABLE) cudaDeviceSynchronize();
+        cleanout_task(d, t, st);
+        if (st->done) d->event_pool.push_back(st->done);
+        delete st;
+        t->reserved[0] = nullptr;
+    }
+    return rc;
+}
+
 // pop (:2196-2359) + epilog (:2364-2453) bookkeeping once the device work is really done
-static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t) {
+static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     for (int i = 0; i < t->nb_flows; ++i) {
         const uint8_t type = t->flow_access[i];
         if (!(type & PB2_FLOW_ACCESS_RW) || !t->flow_data[i]) continue;
@@ -779,6 +1059,7 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t) {
         }
         trace(d, t, i, EV_EPILOG, 0);
     }
+    release_peer_sources(d, st, t->nb_flows);
     if (t->task_type == 0) d->stats.executed_tasks++;
     // the generated complete_hook bumps data_out->version of every WRITE flow (jdf2c.c:7102); data_out is the
     // host copy after the epilog.  It runs inside the runtime's completion, i.e. inside t->complete; the trace
@@ -810,10 +1091,10 @@ static bool progress_completions(pb2_device_s* d, bool* drained) {
                 continue;
             }
             pb2_gpu_task_t* t = f.task;
-            finish_task(d, t);
+            finish_task(d, t, f.st);
             delete f.st;
             t->reserved[0] = nullptr;
-            if (t->complete) t->complete(t, d->failed ? PB2_HOOK_RETURN_ERROR : PB2_HOOK_RETURN_DONE, t->complete_cookie);
+            if (t->complete) t->complete(t, d->failed ? PB2_HOOK_RETURN_DISABLE : PB2_HOOK_RETURN_DONE, t->complete_cookie);
             if (d->params.trace_events)
                 for (int i = 0; i < t->nb_flows; ++i)
                     if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && t->flow_data[i]) trace(d, t, i, EV_COMPLETE, 0);
@@ -829,13 +1110,18 @@ static bool progress_completions(pb2_device_s* d, bool* drained) {
 
 static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task);
 
+static void push_pending(pb2_device_s* d, pb2_gpu_task_t* task) {
+    std::lock_guard<std::mutex> g(d->pending_lock);
+    d->pending.push_back({task, d->params.use_priorities ? task->priority : 0, d->pending_seq++});
+    std::push_heap(d->pending.begin(), d->pending.end());
+}
+
 extern "C" int pb2_kernel_scheduler(pb2_device_t* d, pb2_gpu_task_t* task) {
     if (!d || !task) return PB2_HOOK_RETURN_ERROR;
     if (d->failed) return PB2_HOOK_RETURN_DISABLE;
     int32_t rc = d->mutex.fetch_add(1);
     if (rc > 0) {  // somebody manages this GPU: hand the task over (:2586-2589)
-        std::lock_guard<std::mutex> g(d->pending_lock);
-        d->pending.push_back(task);
+        push_pending(d, task);
         return PB2_HOOK_RETURN_ASYNC;
     }
     return manager_loop(d, task);
@@ -859,6 +1145,41 @@ extern "C" int pb2_device_manage(pb2_device_t* d) {
     return rc == PB2_HOOK_RETURN_ASYNC ? PB2_SUCCESS : PB2_ERR_DEVICE;
 }
 
+// next pending task (caller holds pending_lock): the top of the heap, or with sort_pending_tasks the one among the
+// ten best that has to bring in the fewest tiles (parsec_gpu_sort_pending_list, device_gpu.c:117-166)
+static pb2_gpu_task_t* pop_pending(pb2_device_s* d) {
+    if (d->pending.empty()) return nullptr;
+    auto pop_top = [d]() {
+        std::pop_heap(d->pending.begin(), d->pending.end());
+        pb2_device_s::Pending p = d->pending.back();
+        d->pending.pop_back();
+        return p;
+    };
+    if (!d->params.sort_pending_tasks) return pop_top().task;
+    std::vector<pb2_device_s::Pending> head;
+    const size_t span = std::min<size_t>(10, d->pending.size());
+    for (size_t i = 0; i < span; ++i) head.push_back(pop_top());
+    size_t pick = 0;
+    int best = 1 << 30;
+    for (size_t i = 0; i < head.size(); ++i) {
+        const pb2_gpu_task_t* c = head[i].task;
+        int missing = 0;
+        for (int f = 0; f < c->nb_flows; ++f)
+            if (c->flow_data[f] && (c->flow_access[f] & PB2_FLOW_ACCESS_RW) && !c->flow_data[f]->device_copies[d->device_index])
+                ++missing;
+        if (missing < best) {
+            best = missing;
+            pick = i;
+        }
+    }
+    for (size_t i = 0; i < head.size(); ++i)
+        if (i != pick) {
+            d->pending.push_back(head[i]);
+            std::push_heap(d->pending.begin(), d->pending.end());
+        }
+    return head[pick].task;
+}
+
 static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
     // this thread is the manager until the device drains
     if (cudaSetDevice(d->cuda_index) != cudaSuccess) {
@@ -873,6 +1194,7 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
     const auto leave = [d]() { return d->failed ? PB2_HOOK_RETURN_DISABLE : PB2_HOOK_RETURN_ASYNC; };
     while (true) {
         bool progressed = false;
+        drain_peer_unpins(d);
         // 1. stalled tasks go first (they hold the oldest priorities), then the new one
         if (cur == nullptr && !d->stalled.empty() && d->inflight_count < max_inflight) {
             cur = d->stalled.front();
@@ -882,32 +1204,11 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
             std::lock_guard<std::mutex> g(d->pending_lock);
             while (!d->deferred.empty()) {  // queued while nobody managed the device: they count from now on
                 d->mutex.fetch_add(1);
-                d->pending.push_back(d->deferred.front());
+                d->pending.push_back({d->deferred.front(), 0, d->pending_seq++});
+                std::push_heap(d->pending.begin(), d->pending.end());
                 d->deferred.pop_front();
             }
-            if (!d->pending.empty()) {
-                size_t pick = 0;
-                if (d->params.sort_pending_tasks) {
-                    // parsec_gpu_sort_pending_list: look at the first 10 and prefer the task that has to bring in the
-                    // fewest tiles (parsec_gpu_check_space_needed counts flows without a device copy)
-                    int best = 1 << 30;
-                    const size_t span = std::min<size_t>(10, d->pending.size());
-                    for (size_t i = 0; i < span; ++i) {
-                        const pb2_gpu_task_t* c = d->pending[i];
-                        int missing = 0;
-                        for (int f = 0; f < c->nb_flows; ++f)
-                            if (c->flow_data[f] && (c->flow_access[f] & PB2_FLOW_ACCESS_RW) &&
-                                !c->flow_data[f]->device_copies[d->device_index])
-                                ++missing;
-                        if (missing < best) {
-                            best = missing;
-                            pick = i;
-                        }
-                    }
-                }
-                cur = d->pending[pick];
-                d->pending.erase(d->pending.begin() + pick);
-            }
+            cur = pop_pending(d);
         }
         if (cur) {
             auto ts0 = std::chrono::steady_clock::now();
@@ -925,10 +1226,17 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
                 // no room: write dirty tiles back so that they become evictable, then wait for completions
                 bool w = start_w2r(d);
                 if (!w && d->inflight_count == 0) {
+                    std::unique_lock<std::mutex> pk(d->peer_lock);
+                    const bool peers_hold_tiles = !d->peer_unpins.empty();
+                    pk.unlock();
+                    if (peers_hold_tiles) {  // readers handed back by a peer GPU: take them in and try again
+                        d->stalled.push_front(cur);
+                        cur = nullptr;
+                        continue;
+                    }
                     fprintf(stderr,
                             "[parsec_b200] task needs more device memory than can ever be freed (%zu bytes in use)\n",
                             d->heap->in_use());
-                    d->failed = true;
                     if (cur->complete) cur->complete(cur, PB2_HOOK_RETURN_ERROR, cur->complete_cookie);
                     free(cur);
                     if (d->mutex.fetch_sub(1) == 1) return leave();
@@ -936,22 +1244,20 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
                 } else {
                     d->stalled.push_front(cur);
                     cur = nullptr;
-                    // block until something completes, otherwise we would spin on the same failure
-                    while (!progress_completions(d, &drained)) {
-                    }
+                    // wait until something completes, otherwise we would spin on the same failure; yield the core
+                    // between polls (one manager thread per GPU shares the host with the submitters)
+                    while (!progress_completions(d, &drained)) std::this_thread::yield();
                     if (drained) return leave();
                     progressed = true;
                 }
             } else {
-                d->failed = true;
-                if (cur->reserved[0]) {
-                    delete (TaskState*)cur->reserved[0];
-                    cur->reserved[0] = nullptr;
-                }
+                // the task does not run here (stage-in already taken back by try_submit); the device itself is
+                // only lost when a CUDA call failed
                 if (cur->complete) cur->complete(cur, r, cur->complete_cookie);
                 free(cur);
                 if (d->mutex.fetch_sub(1) == 1) return leave();
                 cur = nullptr;
+                progressed = true;
             }
         }
         // 2. retire whatever finished
@@ -1007,8 +1313,7 @@ extern "C" int pb2_device_data_advise(pb2_device_t* d, pb2_data_t* data, int adv
                         return PB2_SUCCESS;
                     }
                     if (d->mutex.compare_exchange_weak(cur, cur + 1)) {
-                        std::lock_guard<std::mutex> g(d->pending_lock);
-                        d->pending.push_back(t);
+                        push_pending(d, t);
                         return PB2_SUCCESS;
                     }
                 }
@@ -1070,16 +1375,19 @@ extern "C" int pb2_device_pin_for_read(pb2_device_t* d, pb2_data_t* data, void**
     t.locals[2] = -1;
     if (reserve_device_space(d, &t) != 0) return PB2_ERR_OUT_OF_RESOURCE;
     TaskState st;
+    st.host_source_only = true;
     bool issued = false;
     if (stage_in_flow(d, &t, &st, 0, &issued) < 0) return PB2_ERROR;
     if (issued) {
-        d->h2d_seq++;
-        cudaEventRecord(d->h2d_events[d->h2d_seq % EVENT_RING], d->h2d);
+        const uint64_t seq = d->h2d_seq.load() + 1;
+        cudaEventRecord(d->h2d_events[seq % EVENT_RING], d->h2d);
+        d->h2d_seq.store(seq);
         complete_push_flow(d, &t, 0);
     }
     pb2_copy_t* c = data->device_copies[d->device_index];
     if (wait_stream && c->ready_seq) {
-        uint64_t w = (d->h2d_seq - c->ready_seq >= (uint64_t)EVENT_RING) ? d->h2d_seq : c->ready_seq;
+        const uint64_t now = d->h2d_seq.load();
+        uint64_t w = (now - c->ready_seq >= (uint64_t)EVENT_RING) ? now : c->ready_seq;
         cudaStreamWaitEvent((cudaStream_t)wait_stream, d->h2d_events[w % EVENT_RING], 0);
     }
     if (wait_stream && c->ready_event) cudaStreamWaitEvent((cudaStream_t)wait_stream, c->ready_event, 0);
@@ -1115,6 +1423,7 @@ extern "C" int pb2_device_adopt_remote(pb2_device_t* d, pb2_data_t* data, uint32
     c->device_index = (int8_t)d->device_index;
     c->original = data;
     data->device_copies[d->device_index] = c;
+    d->all_copies.insert(c);
     data->host_copy.version = version;
     data->host_copy.coherency_state = PB2_DATA_COHERENCY_SHARED;
     d->stats.data_in_from_peers += data->nb_elts;
@@ -1138,6 +1447,17 @@ extern "C" int pb2_device_drop_remote(pb2_device_t* d, pb2_data_t* data) {
     return PB2_SUCCESS;
 }
 
+// public form of the same, for the overlay shim: the runtime has destroyed the data this copy belonged to
+extern "C" int pb2_device_drop_copy(pb2_device_t* d, pb2_data_t* data) {
+    if (!d || !data) return PB2_ERR_BAD_PARAM;
+    drain_peer_unpins(d);
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (!c) return PB2_ERR_NOT_FOUND;
+    release_copy(d, c);
+    return PB2_SUCCESS;
+}
+
+extern "C" size_t pb2_device_heap_capacity(pb2_device_t* d) { return d && d->heap ? d->heap->capacity() : 0; }
 extern "C" int pb2_device_exec_streams(pb2_device_t* d) { return d ? (int)d->exec.size() : 0; }
 
 // ------------------------------------------------------------------------------------ per-stream workspace (a19)

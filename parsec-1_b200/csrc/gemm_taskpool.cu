@@ -27,6 +27,9 @@ int pb2_matrix_geometry(const pb2_matrix_block_cyclic_t* dc, int* out);
 void* pb2_comm_stream(pb2_comm_t* c);
 int pb2_comm_group_begin(pb2_comm_t* c);
 int pb2_comm_group_end(pb2_comm_t* c);
+int pb2_comm_agree(pb2_comm_t* c, int ok);
+int pb2_comm_abort(pb2_comm_t* c);
+size_t pb2_device_heap_capacity(pb2_device_t* d);
 int pb2_comm_geometry(const pb2_comm_t* c, int* out);
 int pb2_device_pin_for_read(pb2_device_t* d, pb2_data_t* data, void** dev_ptr, void* wait_stream);
 int pb2_device_unpin(pb2_device_t* d, pb2_data_t* data);
@@ -67,6 +70,11 @@ struct pb2_taskpool_s {
     std::vector<pb2_data_s*> a_tiles, b_tiles;
     std::vector<int> row_slot, col_slot;
     std::vector<pb2_data_s*> proxies, pinned;
+    // consumers still to retire for each received (proxy) tile: A(m,k) feeds one GEMM per local tile column, B(k,n) one per
+    // local tile row.  When the count reaches zero the HBM slot goes back to the heap, so that what a rank holds of the
+    // other ranks' operands is bounded by the broadcast lookahead instead of growing with the whole taskpool.
+    std::vector<int32_t> a_left, b_left;   // -1 = a tile this rank owns
+    int64_t dropped = 0;
     std::vector<cudaEvent_t> comm_events;
     // the broadcast plan (canonical order, k ascending) and how far it has been issued.  Group k is issued no later than
     // the moment the first GEMM of step k - bcast_lookahead is spawned, so a root's stage-in of the tiles it
@@ -160,6 +168,11 @@ static void on_complete(pb2_gpu_task_t* t, int status, void* cookie) {
     }
     tp->nb_gemm++;
     const int m = (int)t->locals[0], n = (int)t->locals[1], k = (int)t->locals[2];
+    if (!tp->a_left.empty()) {  // P x Q: give received operands back once their last local reader has retired
+        const size_t ia = (size_t)tp->row_slot[m] * tp->KT + k, ib = (size_t)tp->col_slot[n] * tp->KT + k;
+        if (tp->a_left[ia] > 0 && --tp->a_left[ia] == 0 && pb2_device_drop_remote(tp->dev, tp->a_tiles[ia]) == PB2_SUCCESS) tp->dropped++;
+        if (tp->b_left[ib] > 0 && --tp->b_left[ib] == 0 && pb2_device_drop_remote(tp->dev, tp->b_tiles[ib]) == PB2_SUCCESS) tp->dropped++;
+    }
     if (tp->status) return;
     if (k + 1 < tp->KT) {
         int rc = spawn_gemm(tp, m, n, k + 1);  // release_deps: C GEMM(m,n,k) -> C GEMM(m,n,k+1)
@@ -243,9 +256,9 @@ static int issue_plan_upto(pb2_taskpool_s* tp, int k_limit) {
     std::vector<pb2_data_s*> group;  // received tiles waiting for their group's event
     while (tp->plan_pos < tp->plan.size() && tp->plan[tp->plan_pos].k < k_limit) {
         const int k = tp->plan[tp->plan_pos].k;
-        pb2_comm_group_begin(tp->comm);  // one fused launch per communicator for the whole GEMM step
+        int rc = pb2_comm_group_begin(tp->comm);  // one fused launch per communicator for the whole GEMM step
+        if (rc != PB2_SUCCESS) return rc;
         group.clear();
-        int rc = PB2_SUCCESS;
         for (; rc == PB2_SUCCESS && tp->plan_pos < tp->plan.size() && tp->plan[tp->plan_pos].k == k; ++tp->plan_pos) {
             const pb2_bcast_op_t& op = tp->plan[tp->plan_pos];
             pb2_data_s* d = op.which == 0 ? a_tile(tp, op.idx, op.k) : b_tile(tp, op.k, op.idx);
@@ -264,8 +277,11 @@ static int issue_plan_upto(pb2_taskpool_s* tp, int k_limit) {
             }
             rc = pb2_comm_bcast(tp->comm, op.which, ptr, d->nb_elts, op.root);
         }
-        pb2_comm_group_end(tp->comm);
-        if (!group.empty()) {
+        {
+            int erc = pb2_comm_group_end(tp->comm);
+            if (rc == PB2_SUCCESS) rc = erc;
+        }
+        if (rc == PB2_SUCCESS && !group.empty()) {
             cudaEvent_t e;
             cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
             cudaEventRecord(e, cs);
@@ -307,7 +323,26 @@ static int prepare_operands(pb2_taskpool_s* tp) {
         }
     tp->plan.clear();
     tp->plan_pos = 0;
+    tp->a_left.clear();
+    tp->b_left.clear();
+    tp->dropped = 0;
     if (tp->P * tp->Q == 1) return PB2_SUCCESS;
+    tp->a_left.assign(tp->a_tiles.size(), -1);
+    tp->b_left.assign(tp->b_tiles.size(), -1);
+    for (int m = 0; m < tp->MT; ++m)
+        for (int k = 0; k < tp->KT && tp->row_slot[m] >= 0; ++k)
+            if (!pb2_matrix_data_of(tp->A, m, k)) {  // a proxy: read by GEMM(m, n, k) for every local C tile of tile row m
+                int readers = 0;
+                for (int n = 0; n < tp->NT; ++n) readers += pb2_matrix_rank_of(tp->C, m, n) == tp->gC.rank;
+                tp->a_left[(size_t)tp->row_slot[m] * tp->KT + k] = readers;
+            }
+    for (int n = 0; n < tp->NT; ++n)
+        for (int k = 0; k < tp->KT && tp->col_slot[n] >= 0; ++k)
+            if (!pb2_matrix_data_of(tp->B, k, n)) {
+                int readers = 0;
+                for (int m = 0; m < tp->MT; ++m) readers += pb2_matrix_rank_of(tp->C, m, n) == tp->gC.rank;
+                tp->b_left[(size_t)tp->col_slot[n] * tp->KT + k] = readers;
+            }
     // READ tasks of tiles that only feed remote GEMMs still execute on their owner: count the owned tiles outside the
     // rows / columns walked above (none on a grid where every rank owns C tiles in each of its rows and columns).
     int64_t nops = pb2_comm_plan_ex(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, tp->gC.kp, tp->gC.kq, tp->gA.kq,
@@ -316,6 +351,20 @@ static int prepare_operands(pb2_taskpool_s* tp) {
     tp->plan.resize((size_t)nops);
     pb2_comm_plan_ex(tp->P, tp->Q, tp->gC.rank, tp->MT, tp->NT, tp->KT, tp->gC.kp, tp->gC.kq, tp->gA.kq, tp->gB.kp,
                      tp->gC.ip, tp->gC.jq, tp->plan.data(), nops);
+    // Before the first collective every rank checks that it can hold what the schedule will ask of it -- the operands of
+    // the k-steps in flight (lookahead + the steps the window of chains spans, or all of them with bcast_lookahead = 0)
+    // next to one window of C tiles -- and the grid agrees: a rank that would fail half-way would otherwise leave its
+    // peers blocked inside ncclBroadcast.
+    {
+        const int64_t steps = tp->bcast_lookahead > 0 ? std::min<int64_t>(tp->KT, tp->bcast_lookahead + 2) : tp->KT;
+        const size_t c_bytes = (size_t)tp->gC.mb * tp->gC.nb * tp->gC.es;
+        const size_t need = (size_t)steps * ((size_t)rows * a_bytes + (size_t)cols * b_bytes) + 4 * c_bytes;
+        const bool fits = need <= pb2_device_heap_capacity(tp->dev);
+        if (!fits)
+            fprintf(stderr, "[parsec_b200] rank %d: the HBM heap (%zu bytes) cannot hold %lld k-steps of operands (%zu bytes)\n",
+                    tp->gC.rank, pb2_device_heap_capacity(tp->dev), (long long)steps, need);
+        if (!pb2_comm_agree(tp->comm, fits ? 1 : 0)) return PB2_ERR_OUT_OF_RESOURCE;
+    }
     return issue_plan_upto(tp, tp->bcast_lookahead > 0 ? (int)std::min<int64_t>(tp->bcast_lookahead, tp->KT) : tp->KT);
 }
 
@@ -366,6 +415,11 @@ extern "C" int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats
     if (!tp->status && tp->plan_pos < tp->plan.size()) {  // a rank with no GEMM of its own still serves its broadcasts
         rc = issue_plan_upto(tp, tp->KT);
         if (rc != PB2_SUCCESS) tp->status = rc;
+    }
+    if (tp->status && tp->comm && tp->plan_pos < tp->plan.size()) {
+        // this rank leaves the canonical sequence with broadcasts still owed: make its peers fail instead of hang
+        fprintf(stderr, "[parsec_b200] rank %d aborts its communicators (status %d)\n", tp->gC.rank, tp->status);
+        pb2_comm_abort(tp->comm);
     }
     release_operands(tp);
     auto t1 = std::chrono::steady_clock::now();

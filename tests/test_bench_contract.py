@@ -1,4 +1,5 @@
-"""bench.py's reference arm runs on the CPU (the oracle port on the host cores): check the JSON contract here."""
+"""bench.py's reference arm runs on the CPU -- the reference runtime with CPU task bodies when baseline/_ref is built
+(kind "reference"), else the oracle port (kind "port"): check the JSON contract here."""
 import json
 import os
 import subprocess
@@ -16,7 +17,9 @@ def test_reference_arm_prints_one_json_line_with_the_contract_keys():
     j = json.loads(lines[0])
     assert j["impl"] == "reference" and j["unit"] == "GFLOP/s" and j["higher_is_better"] is True
     assert j["value"] > 0 and j["dtype"] == "f64" and j["vs_baseline"] is None and j["data"] == "synthetic"
-    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["value"] == j["value"]
+    built = os.path.exists(os.path.join(ROOT, "baseline", "_ref", "bin", "dgemm_NN_app"))
+    assert j["cpu_baseline"]["kind"] == ("reference" if built else "port")
+    assert j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["value"] == j["value"]
     assert j["e2e"] == {"value": j["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in j["config"] and "model" not in j["config"]
 

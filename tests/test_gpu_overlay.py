@@ -153,3 +153,44 @@ def test_stock_reference_module_runs_the_same_binary(tmp_path):
     out, err = run_app("stock", ["-N", 2048, "-t", 256, "-c", 4, "--dump", dump])
     assert out["gpus"] == 1, err[-2000:]
     check_against_oracle(out, dump, 2048, 256)
+
+
+def test_declined_bodies_fall_back_to_the_cpu_incarnation(tmp_path):
+    """Step k = 3 of every chain is declined by the CUDA body (PARSEC_HOOK_RETURN_NEXT): the module takes the task's
+    stage-in back, writes the chain's dirty C tile home, and the runtime runs the CPU incarnation on current host data
+    (device_cuda_module.c:2644-2656, :2472-2526 -- the reference leaves the host copy stale there).  The chain then
+    goes back to the GPU, which must notice that the host copy is the newer one."""
+    _need_binaries()
+    N, NB, k = 2048, 256, 3
+    dump = str(tmp_path / "C.bin")
+    out, err = run_app("overlay", ["-N", N, "-t", NB, "-c", 4, "--decline", k, "--dump", dump])
+    assert out["gpus"] == 1, err[-2000:]
+    d, A, B, Cref, cnt, ver = oracle_result(N, NB)
+    chains = (N // NB) ** 2
+    assert out["gemm_cpu"] == chains and out["gemm_gpu"] == cnt.gemm - chains
+    assert out["device_executed_tasks"] == cnt.gemm - chains
+    assert out["c_version_min"] == out["c_version_max"] == N // NB
+    got = np.fromfile(dump, dtype=np.float64)
+    dense = lambda m: O.tiled_to_dense(d, m)
+    assert O.parity_norm(dense(got), dense(Cref), dense(A), dense(B), N) < 10.0
+
+
+def test_two_gpus_in_one_process_share_tiles_over_nvlink(tmp_path):
+    """--mca device_cuda_enabled 2: the runtime spreads the C chains over two device modules of one process
+    (parsec_get_best_device); A and B tiles wanted by both GPUs are staged once from the host and once from the peer
+    (device_cuda_module.c:1310-1378), the nvlink.jdf pattern."""
+    _need_binaries()
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    N, NB = 4096, 256
+    dump = str(tmp_path / "C.bin")
+    out, err = run_app("overlay", ["-N", N, "-t", NB, "-c", 6, "--dump", dump], mca=("device_cuda_enabled", "2"))
+    assert out["gpus"] == 2, err[-2000:]
+    norm = check_against_oracle(out, dump, N, NB)
+    tile = NB * NB * 8
+    tiles = 3 * (N // NB) ** 2
+    assert out["d2d_bytes"] > 0                                   # some operand tiles came from the peer GPU
+    assert out["h2d_bytes"] + out["d2d_bytes"] >= tiles * tile    # every tile was staged at least once
+    assert out["h2d_bytes"] < 2 * tiles * tile                    # and the host was not asked twice for everything
+    print("2 GPUs, one process: h2d %.0f MiB, d2d %.0f MiB, norm %.3g" % (out["h2d_bytes"] / 2 ** 20, out["d2d_bytes"] / 2 ** 20, norm))
