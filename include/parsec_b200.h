@@ -81,6 +81,15 @@ int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, f
 int parsec_b200_gemm_tf32_sm100(char transa, char transb, int m, int n, int k, float alpha, const float* A, int lda,
                                 const float* B, int ldb, float beta, float* C, int ldc, void* stream);
 
+/* Batches.  The bf16 / tf32 GEMM calls one thread makes on `stream` between parsec_b200_batch_begin and
+ * parsec_b200_batch_end are recorded and launched together as one grouped persistent kernel (at _end, or every 16
+ * calls): the tile tasks a task runtime has ready at the same time share one launch, whose CTA pairs walk the output
+ * tiles of all of them with the epilogue of one tile under the MMAs of the next.  The reference has no counterpart
+ * (its bodies launch one cuBLAS call per task, nvlink.jdf:142); the device module brackets the bodies it submits
+ * together with these calls, so bodies need no change.  Results are those of the single calls. */
+int parsec_b200_batch_begin(void* stream);
+int parsec_b200_batch_end(void* stream);
+
 /* HBM heap: the job of zone_malloc_init / zone_malloc / zone_free / zone_in_use (parsec/utils/zone_malloc.h:41-63) --
  * carve the module's one device allocation into tiles, in units of `unit_size` bytes -- with a policy of its own: a
  * freed extent waits on a stack of extents of its size and is handed to the next request of that size (O(1) both

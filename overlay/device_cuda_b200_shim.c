@@ -391,6 +391,9 @@ static void b200_complete(pb2_gpu_task_t *t, int status, void *cookie)
                 break;
             }
         }
+        /* its inputs are looked up already: a second prepare_input would forget which repository entries it consumed */
+        task->status = PARSEC_TASK_STATUS_HOOK;
+        PARSEC_LIST_ITEM_SINGLETON(task);
         __parsec_reschedule(es, task);
         return;
     }

@@ -28,6 +28,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <vector>
 
 #include "pb2_internal.h"
@@ -568,6 +569,274 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Grouped persistent variant: ONE launch runs a group of independent GEMMs (the tile tasks the device module has ready
+// at the same time), one CTA pair per TPC, each pair walking the 256 x 256 output tiles of the whole group.
+//
+// Why: a 2048^3 tile task is 64 output tiles for 74 CTA pairs, and with one launch per task the C tile of every task
+// streams in and out while its CTAs' tensor cores idle (7 us of set-up + epilogue per 26 us CTA lifetime,
+// profiles/umma_trace_r1.md).  Here
+//   * the accumulator is double buffered in TMEM (2 x 256 columns = the whole TMEM of the SM): the MMA warp starts the
+//     next tile while the four epilogue warps drain the previous one, whatever task either belongs to;
+//   * the epilogue has its own shared-memory boxes (the operand ring is never idle any more), the old C boxes of the
+//     next tile are requested while its MMAs run;
+//   * set-up (barriers, TMEM allocation, cluster rendez-vous) is paid once per launch, not once per tile;
+//   * tiles are walked in a grouped raster (8 tile rows at a time), so that the A and B panels the pairs touch together
+//     fit in L2 for a large GEMM (the column-major walk of the per-tile kernel re-read them ~3x from DRAM at 8192^3).
+// Tensor maps travel in the kernel parameter space (one __grid_constant__ struct), like the per-tile kernels' do.
+constexpr int Q_STAGES = 5;          // operand ring: 5 x 32 KiB
+constexpr int Q_EBUF = 3;            // C boxes (32 x 32 fp32) per epilogue warp
+constexpr int Q_RASTER = 8;          // tile rows per raster group
+constexpr int Q_TMEM_COLS = 512;     // two accumulator stages
+constexpr size_t grouped_smem() {
+    return (size_t)Q_STAGES * P_STAGE_BYTES + 4 * Q_EBUF * E_BOX_BYTES + 1024 + 1024;
+}
+
+struct UmmaTask {
+    CUtensorMap mapA, mapBh, mapC;
+    float* C;
+    int M, N, K, ldc;
+    float alpha, beta;
+    int pairs_m, tiles_n;   // 256-row and 256-column tiles of this GEMM
+    int tile_begin;         // index of its first tile in the group's walk
+    int pad_;
+};
+template <int MAXT>
+struct UmmaGroup {
+    UmmaTask t[MAXT];
+    int ntasks, total_tiles;
+};
+
+struct TileRef {
+    int task, m0, n0, kt;  // m0: first row of the PAIR's tile (this CTA adds rank * 128)
+};
+template <int MAXT, int EB>
+__device__ __forceinline__ TileRef decode_tile(const UmmaGroup<MAXT>& g, int tile) {
+    int t = 0;
+#pragma unroll 1
+    while (t + 1 < g.ntasks && tile >= g.t[t + 1].tile_begin) ++t;
+    const UmmaTask& k = g.t[t];
+    const int local = tile - k.tile_begin;
+    const int per_group = Q_RASTER * k.tiles_n;
+    const int first = (local / per_group) * Q_RASTER;
+    const int rows = min(Q_RASTER, k.pairs_m - first);
+    const int in_group = local % per_group;
+    TileRef r;
+    r.task = t;
+    r.m0 = (first + in_group % rows) * (2 * G_BM);
+    r.n0 = (in_group / rows) * G_BN;
+    r.kt = (k.K + 128 / EB - 1) / (128 / EB);
+    return r;
+}
+
+// arrive on the barrier at the same offset in CTA `target_rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t target_rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(smem_u32(bar)), "r"(target_rank));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(remote) : "memory");
+}
+
+template <int MAXT, int EB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G_THREADS, 1)
+gemm_umma_grouped(const __grid_constant__ UmmaGroup<MAXT> g) {
+    constexpr int BKE = 128 / EB;
+    constexpr int MBOX = 128 / EB;
+    constexpr int NBOX = G_BM / MBOX;
+    constexpr int BOX_BYTES = BKE * 128;
+    constexpr int UK = 32 / EB;
+    constexpr uint32_t IDESC = (1u << 4) | ((EB == 2 ? 1u : 2u) << 7) | ((EB == 2 ? 1u : 2u) << 10) | (1u << 15) |
+                               ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)((2 * G_BM) >> 4) << 24);
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase0 = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (sbase0 - raw);
+    uint8_t* ebufs = smem + Q_STAGES * P_STAGE_BYTES;                   // 4 warps x Q_EBUF boxes
+    uint64_t* full = reinterpret_cast<uint64_t*>(ebufs + 4 * Q_EBUF * E_BOX_BYTES);
+    uint64_t* empty = full + Q_STAGES;
+    uint64_t* acc_full = empty + Q_STAGES;     // [2] accumulator stage complete (multicast commit, both CTAs)
+    uint64_t* acc_empty = acc_full + 2;        // [2] accumulator stage drained: 8 arrivals on the LEADER's barrier
+    uint64_t* cbar = acc_empty + 2;            // [4][Q_EBUF] C boxes landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cbar + 4 * Q_EBUF);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < Q_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&acc_full[a], 1);
+            mbar_init(&acc_empty[a], 8);
+        }
+        for (int i = 0; i < 4 * Q_EBUF; ++i) mbar_init(&cbar[i], 1);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)Q_TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::);
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer (one lane per CTA)
+        if (lane == 0) {
+            int stage = 0, last_task = -1;
+            uint32_t phase = 0;
+            long long it = 0;
+            for (int tile = pair; tile < g.total_tiles; tile += npairs) {
+                const TileRef r = decode_tile<MAXT, EB>(g, tile);
+                const UmmaTask& k = g.t[r.task];
+                if (r.task != last_task) {
+                    tma_prefetch_desc(&k.mapA);
+                    tma_prefetch_desc(&k.mapBh);
+                    last_task = r.task;
+                }
+                const int m0 = r.m0 + rank * G_BM;
+                for (int kt = 0; kt < r.kt; ++kt, ++it) {
+                    if (it >= Q_STAGES) mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * P_STAGE_BYTES;
+                    if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * P_STAGE_BYTES);
+                    const uint32_t lead_full = smem_u32(&full[stage]) & 0xFEFFFFFFu;
+#pragma unroll
+                    for (int b = 0; b < NBOX; ++b)
+                        tma_load_2d_pair(sa + b * BOX_BYTES, &k.mapA, m0 + b * MBOX, kt * BKE, lead_full);
+                    tma_load_2d_pair(sa + G_A_BYTES, &k.mapBh, kt * BKE, r.n0 + rank * (G_BN / 2), lead_full);
+                    if (++stage == Q_STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (leader CTA, one lane)
+        if (lane == 0 && rank == 0) {
+            int stage = 0, i = 0;
+            uint32_t phase = 0;
+            for (int tile = pair; tile < g.total_tiles; tile += npairs, ++i) {
+                const TileRef r = decode_tile<MAXT, EB>(g, tile);
+                const int a = i & 1;
+                if (i >= 2) {  // both CTAs' epilogues must have drained this accumulator stage
+                    mbar_wait(&acc_empty[a], (uint32_t)((i >> 1) - 1) & 1u);
+                    tc_fence_after();
+                }
+                const uint32_t tmem_d = tmem_base + (uint32_t)(a * G_TMEM_COLS);
+                for (int kt = 0; kt < r.kt; ++kt) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = sbase0 + stage * P_STAGE_BYTES;
+                    const uint32_t sb = sa + G_A_BYTES;
+#pragma unroll
+                    for (int ku = 0; ku < BKE / UK; ++ku) {
+                        const uint64_t adesc = EB == 2 ? umma_desc(sa + ku * UK * 128, BOX_BYTES, 1024, 2)
+                                                       : umma_desc(sa + ku * UK * 128, BOX_BYTES, 512, 1);
+                        const uint64_t bdesc = umma_desc(sb + ku * 32, 16, 1024);
+                        umma_pair<EB>(tmem_d, adesc, bdesc, IDESC, (kt | ku) != 0);
+                    }
+                    umma_commit_pair(&empty[stage]);
+                    if (++stage == Q_STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit_pair(&acc_full[a]);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue warps (4 per CTA)
+        const int quarter = warp & 3;
+        float* bufs = reinterpret_cast<float*>(ebufs + quarter * (Q_EBUF * E_BOX_BYTES));
+        uint64_t* bar = cbar + quarter * Q_EBUF;
+        uint32_t loads = 0;  // C boxes requested so far on each buffer decides the parity to wait for: count per buffer
+        uint32_t nload[Q_EBUF];
+#pragma unroll
+        for (int b = 0; b < Q_EBUF; ++b) nload[b] = 0;
+        (void)loads;
+        int i = 0, last_task = -1;
+        for (int tile = pair; tile < g.total_tiles; tile += npairs, ++i) {
+            const TileRef r = decode_tile<MAXT, EB>(g, tile);
+            const UmmaTask& k = g.t[r.task];
+            const int a = i & 1;
+            const int row0 = r.m0 + rank * G_BM + quarter * 32;
+            const bool live = row0 < k.M;  // warp-uniform (n0 < N always: the tile exists)
+            const int nchunks = live ? (min(G_BN, k.N - r.n0) + 31) / 32 : 0;
+            const bool readc = k.beta != 0.0f;
+            const float alpha = k.alpha, beta = k.beta;
+            if (lane == 0 && r.task != last_task) tma_prefetch_desc(&k.mapC);
+            last_task = r.task;
+            // the old C boxes of this tile are requested now, while its MMAs still run; the stores of the previous tile
+            // must be done reading the buffers first
+            if (readc && nchunks > 0 && lane == 0) {
+                tma_store_wait_read<0>();
+                for (int c = 0; c < nchunks && c < Q_EBUF; ++c) {
+                    mbar_arrive_expect_tx(&bar[c], E_BOX_BYTES);
+                    tma_load_2d(bufs + c * (E_BOX_BYTES / 4), &k.mapC, row0, r.n0 + 32 * c, &bar[c]);
+                }
+            }
+            mbar_wait(&acc_full[a], (uint32_t)(i >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t tmem_acc = tmem_base + (uint32_t)(a * G_TMEM_COLS) + ((uint32_t)(quarter * 32) << 16);
+            if (!live) {  // rows beyond M: nothing to write, but the accumulator stage still has to be handed back
+                tc_fence_before();
+                if (lane == 0) mbar_arrive_cluster(&acc_empty[a], 0);
+                continue;
+            }
+#pragma unroll 1
+            for (int c = 0; c < nchunks; ++c) {
+                const int b = c % Q_EBUF;
+                float* buf = bufs + b * (E_BOX_BYTES / 4);
+                uint32_t v[32];
+                tmem_ld32(tmem_acc + (uint32_t)(32 * c), v);
+                if (c == nchunks - 1) {  // last read of this accumulator stage by this warp: the MMA warp may reuse it
+                    tc_fence_before();
+                    if (lane == 0) mbar_arrive_cluster(&acc_empty[a], 0);
+                }
+                if (readc) {
+                    mbar_wait(&bar[b], nload[b] & 1u);
+                    nload[b]++;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) buf[j * 32 + lane] = alpha * __uint_as_float(v[j]) + beta * buf[j * 32 + lane];
+                } else {
+                    if (lane == 0) tma_store_wait_read<Q_EBUF - 1>();  // the store that last read this buffer is done with it
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) buf[j * 32 + lane] = alpha * __uint_as_float(v[j]);
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&k.mapC, buf, row0, r.n0 + 32 * c);
+                    tma_store_commit();
+                    if (readc && c + Q_EBUF < nchunks) {  // recycle the buffer for the box Q_EBUF chunks ahead
+                        tma_store_wait_read<0>();
+                        mbar_arrive_expect_tx(&bar[b], E_BOX_BYTES);
+                        tma_load_2d(buf, &k.mapC, row0, r.n0 + 32 * (c + Q_EBUF), &bar[b]);
+                    }
+                }
+                // nload is per lane but only its parity is used, and every lane counts the same waits
+            }
+        }
+        if (lane == 0) tma_store_wait_all();
+        __syncwarp();
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();  // the peer's MMAs read this CTA's shared memory; TMEM is freed as a pair
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"((uint32_t)Q_TMEM_COLS));
+    }
+}
+
 struct BfMapKey {
     const void* p;
     int d0, d1, ld, kind;
@@ -606,6 +875,82 @@ static int umma_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, in
     return 0;
 }
 
+// ---- host side of the grouped kernel -------------------------------------------------------------------------------
+constexpr int Q_MAX_GROUP = 16;  // GEMMs per launch: 16 x 448 bytes of tasks in the kernel parameter space
+
+// pairs that can be resident at once (one per TPC whose two SMs are both free for a 2-CTA cluster)
+template <typename K>
+static int resident_pairs(K kernel, int dev) {
+    static int cached[64] = {0};
+    if (dev >= 0 && dev < 64 && cached[dev]) return cached[dev];
+    int pairs = 0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) pairs = prop.multiProcessorCount / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * (pairs > 0 ? pairs : 74));
+    cfg.blockDim = dim3(G_THREADS);
+    cfg.dynamicSmemBytes = grouped_smem();
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) == cudaSuccess && clusters > 0) pairs = clusters;
+    else cudaGetLastError();
+    if (pairs <= 0) pairs = 74;
+    if (dev >= 0 && dev < 64) cached[dev] = pairs;
+    return pairs;
+}
+
+template <int MAXT, int EB>
+static int launch_group_n(const UmmaTask* tasks, int ntasks, int total_tiles, int dev, cudaStream_t stream) {
+    static bool attr_set[64] = {false};
+    auto kernel = gemm_umma_grouped<MAXT, EB>;
+    if (dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)grouped_smem()) != cudaSuccess)
+            return PB2_ERR_CUDA;
+        attr_set[dev] = true;
+    }
+    UmmaGroup<MAXT> g;
+    memcpy(g.t, tasks, sizeof(UmmaTask) * (size_t)ntasks);
+    g.ntasks = ntasks;
+    g.total_tiles = total_tiles;
+    const int pairs = std::min(total_tiles, resident_pairs(kernel, dev));
+    kernel<<<dim3(2 * pairs), G_THREADS, grouped_smem(), stream>>>(g);
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+template <int EB>
+static int launch_group(std::vector<UmmaTask>& tasks, cudaStream_t stream) {
+    if (tasks.empty()) return PB2_SUCCESS;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return PB2_ERR_CUDA;
+    int total = 0;
+    for (UmmaTask& t : tasks) {
+        t.tile_begin = total;
+        total += t.pairs_m * t.tiles_n;
+    }
+    const int n = (int)tasks.size();
+    int rc = n == 1   ? launch_group_n<1, EB>(tasks.data(), n, total, dev, stream)
+             : n <= 4 ? launch_group_n<4, EB>(tasks.data(), n, total, dev, stream)
+                      : launch_group_n<Q_MAX_GROUP, EB>(tasks.data(), n, total, dev, stream);
+    tasks.clear();
+    return rc;
+}
+
+// A batch: the GEMM calls one thread makes on one stream between parsec_b200_batch_begin and _end are collected and
+// launched together (one grouped kernel per element type and per Q_MAX_GROUP calls).
+struct UmmaBatch {
+    bool open = false;
+    void* stream = nullptr;
+    int status = PB2_SUCCESS;
+    std::vector<UmmaTask> bf16, tf32;
+};
+static thread_local UmmaBatch g_batch;
+
 template <int EB>
 static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float alpha, const void* A, int lda, const void* B,
                             int ldb, float beta, float* C, int ldc, void* stream) {
@@ -630,10 +975,11 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
     }
     // PB2_GEMM_BF16_CTAS: 1 = deep single-CTA ring, one CTA per SM; 2 = two independent CTAs per SM;
     // pair = cta_group::2 CTA pairs, two pairs per TPC; pair1 = CTA pairs with the deep ring (kept for A/B runs)
+    // grouped = the persistent grouped kernel (default): one launch per call, or per batch of calls
     static int ctas = -1;
     if (ctas < 0) {
         const char* e = getenv("PB2_GEMM_BF16_CTAS");
-        ctas = !e ? PB2_UMMA_DEFAULT_MODE : !strcmp(e, "1") ? 1 : !strcmp(e, "pair") ? 3 : !strcmp(e, "pair1") ? 4 : 2;
+        ctas = !e ? 5 : !strcmp(e, "grouped") ? 5 : !strcmp(e, "1") ? 1 : !strcmp(e, "pair") ? 3 : !strcmp(e, "pair1") ? 4 : 2;
     }
     CUtensorMap ma, mb;
     if (k > 0 && (umma_tmap(&ma, A, m, k, lda, 0, EB) || umma_tmap(&mb, B, k, n, ldb, ctas >= 3 ? 2 : 1, EB)))
@@ -653,6 +999,27 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
     int c_tma = (!epi_direct && !(((uintptr_t)C) & 15) && !(ldc & 3)) ? 1 : 0;
     if (c_tma && umma_tmap(&mc, C, m, n, ldc, 3, 4)) return PB2_ERR_CUDA;
     if (!c_tma) memset(&mc, 0, sizeof(mc));
+    if (ctas == 5 && (k == 0 || !c_tma)) ctas = 3;  // nothing to multiply, or a C that TMA cannot address: per-tile kernel
+    if (ctas == 5) {
+        UmmaTask t;
+        memset(&t, 0, sizeof(t));
+        t.mapA = ma; t.mapBh = mb; t.mapC = mc;
+        t.C = C; t.M = m; t.N = n; t.K = k; t.ldc = ldc; t.alpha = alpha; t.beta = beta;
+        t.pairs_m = (m + 2 * G_BM - 1) / (2 * G_BM);
+        t.tiles_n = (n + G_BN - 1) / G_BN;
+        if (g_batch.open && g_batch.stream == stream) {  // collected; launched by parsec_b200_batch_end or when full
+            std::vector<UmmaTask>& q = EB == 2 ? g_batch.bf16 : g_batch.tf32;
+            q.push_back(t);
+            if ((int)q.size() == Q_MAX_GROUP) {
+                int rc = launch_group<EB>(q, (cudaStream_t)stream);
+                if (rc != PB2_SUCCESS) g_batch.status = rc;
+                return rc;
+            }
+            return PB2_SUCCESS;
+        }
+        std::vector<UmmaTask> one(1, t);
+        return launch_group<EB>(one, (cudaStream_t)stream);
+    }
     if (ctas >= 3) {
         static bool pair_attr_set[64] = {false};
         if (dev < 64 && !pair_attr_set[dev]) {
@@ -683,6 +1050,26 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
 }
 
 }  // namespace pb2
+
+// Batches: the tile GEMMs a caller has ready at the same time go to the GPU as ONE grouped launch.  Between
+// parsec_b200_batch_begin(stream) and parsec_b200_batch_end(stream) the bf16 / tf32 GEMM calls this thread makes on
+// `stream` are only recorded; _end (or the 16th call) launches them.  The device module brackets the bodies of the
+// tasks it submits together with these two calls, so a JDF body that calls parsec_b200_gemm_bf16 needs no change.
+extern "C" int parsec_b200_batch_begin(void* stream) {
+    if (pb2::g_batch.open) return PB2_ERR_EXISTS;
+    pb2::g_batch.open = true;
+    pb2::g_batch.stream = stream;
+    pb2::g_batch.status = PB2_SUCCESS;
+    return PB2_SUCCESS;
+}
+extern "C" int parsec_b200_batch_end(void* stream) {
+    if (!pb2::g_batch.open || pb2::g_batch.stream != stream) return PB2_ERR_BAD_PARAM;
+    pb2::g_batch.open = false;
+    int rc = pb2::g_batch.status;
+    int r1 = pb2::launch_group<2>(pb2::g_batch.bf16, (cudaStream_t)stream);
+    int r2 = pb2::launch_group<4>(pb2::g_batch.tf32, (cudaStream_t)stream);
+    return rc != PB2_SUCCESS ? rc : r1 != PB2_SUCCESS ? r1 : r2;
+}
 
 extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A,
                                            int lda, const void* B, int ldb, float beta, float* C, int ldc,

@@ -1,4 +1,6 @@
 """tcgen05 / TMEM tile GEMM (bf16 in, fp32 accumulate) through the C ABI against the oracle's bf16 tile GEMM."""
+import os
+
 import numpy as np
 import pytest
 
@@ -97,3 +99,72 @@ def test_unsupported_arguments():
     assert f(b"N", b"N", 8, 8, 8, 1.0, p, 4, p, 8, 1.0, p, 8, 0) == -4     # lda < m
     assert f(b"N", b"N", 12, 8, 8, 1.0, p, 12, p, 8, 1.0, p, 12, 0) == -7  # lda not a multiple of 8 (TMA pitch)
     assert f(b"N", b"N", 0, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8, 0) == 0
+
+
+@pytest.mark.parametrize("variant", ["grouped", "pair"])
+def test_large_gemm_both_kernels_agree_with_cublas(variant, monkeypatch):
+    """4096^3 and a ragged 3000 x 2100 x 1100: many tiles per CTA pair (the persistent walk, both accumulator stages,
+    the raster) against torch.matmul in fp32; PB2_GEMM_BF16_CTAS is read once per process, so the per-tile kernel runs
+    in a child."""
+    import subprocess
+    import sys
+    code = r'''
+import os, sys, numpy as np, torch
+sys.path.insert(0, os.path.join(%r, "tests"))
+from conftest import load_hostapi
+H = load_hostapi()
+for (m, n, k, beta) in [(4096, 4096, 4096, 1.0), (3000, 2100, 1104, 0.0), (512, 8192, 256, 1.0)]:
+    g = torch.Generator(device="cuda"); g.manual_seed(m)
+    A = (torch.rand(k, m, device="cuda", generator=g) - 0.5).to(torch.bfloat16)    # column-major m x k
+    B = (torch.rand(n, k, device="cuda", generator=g) - 0.5).to(torch.bfloat16)    # column-major k x n
+    C = (torch.rand(n, m, device="cuda", generator=g) - 0.5)
+    want = beta * C + (B.float() @ A.float())
+    rc = H.lib().parsec_b200_gemm_bf16_sm100(b"N", b"N", m, n, k, 1.0, A.data_ptr(), m, B.data_ptr(), k, beta, C.data_ptr(), m,
+                                             torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    err = (C - want).abs().max().item()
+    assert err < 2e-3 * max(1.0, k / 1024.0), (m, n, k, err)
+print("ok")
+''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PB2_GEMM_BF16_CTAS=variant)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+def test_batched_calls_give_the_results_of_single_calls():
+    """parsec_b200_batch_begin / _end: 20 GEMMs of mixed shapes, alpha and beta recorded on one stream and launched as
+    grouped kernels (16 + 4), bit-identical to the same calls made one by one."""
+    import torch
+    L = H.lib()
+    L.parsec_b200_batch_begin.argtypes = [H.C.c_void_p]
+    L.parsec_b200_batch_end.argtypes = [H.C.c_void_p]
+    shapes = [(2048, 2048, 2048), (256, 256, 64), (1000, 520, 264), (136, 300, 16), (512, 768, 1024)] * 4
+    g = torch.Generator(device="cuda")
+    g.manual_seed(3)
+    ops = []
+    for i, (m, n, k) in enumerate(shapes):
+        A = (torch.rand(k, m, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
+        B = (torch.rand(n, k, device="cuda", generator=g) - 0.5).to(torch.bfloat16)
+        C = torch.rand(n, m, device="cuda", generator=g) - 0.5
+        ops.append((m, n, k, 1.0 + 0.25 * (i % 3), float(i % 2), A, B, C))
+    s = torch.cuda.current_stream().cuda_stream
+
+    def run(batched):
+        outs = [op[7].clone() for op in ops]
+        if batched:
+            assert L.parsec_b200_batch_begin(s) == 0
+            assert L.parsec_b200_batch_begin(s) != 0            # one batch per thread at a time
+        for (m, n, k, alpha, beta, A, B, _), C in zip(ops, outs):
+            assert L.parsec_b200_gemm_bf16_sm100(b"N", b"N", m, n, k, alpha, A.data_ptr(), m, B.data_ptr(), k, beta,
+                                                 C.data_ptr(), m, s) == 0
+        if batched:
+            assert L.parsec_b200_batch_end(s) == 0
+            assert L.parsec_b200_batch_end(s) != 0              # nothing open any more
+        torch.cuda.synchronize()
+        return outs
+
+    single, batched = run(False), run(True)
+    for a, b, op in zip(single, batched, ops):
+        assert torch.equal(a, b), op[:3]
+        assert not torch.equal(a, op[7])                         # and something was computed

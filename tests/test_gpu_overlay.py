@@ -29,7 +29,7 @@ def _need_binaries():
         pytest.skip("baseline/_ref is not built (overlay/build_overlay.sh needs the reference tree)")
 
 
-def run_app(lib, args, mca=("device_cuda_enabled", "1"), timeout=900):
+def run_app(lib, args, mca=("device_cuda_enabled", "1"), timeout=180):
     env = dict(os.environ)
     env["LD_LIBRARY_PATH"] = os.pathsep.join([os.path.join(REF, lib), os.path.join(ROOT, "parsec-1_b200"),
                                               env.get("LD_LIBRARY_PATH", "")])
