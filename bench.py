@@ -312,6 +312,9 @@ def main():
     ap.add_argument("--inflight", type=int, default=256)
     ap.add_argument("--streams", type=int, default=18, help="h2d + d2h + exec streams (the module spreads a task over as "
                     "many exec streams as its tile size needs: 5 at NB=1024, 16 at NB=512)")
+    ap.add_argument("--batch", type=int, default=-1,
+                    help="tasks per batched submission (one grouped tcgen05 launch per batch); -1 = 16 for --dtype bf16, "
+                         "off for f64 (the DMMA kernel fills the GPU through stream concurrency instead)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the extra checked step after the timed regions")
     ap.add_argument("--hbm-gib", type=float, default=0.0,
@@ -378,6 +381,11 @@ def main():
             peak_tf = live_tf
             peak_src = "measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10 (profiles/fp64_peak_r2.json missing)"
     hbm = {"memory_number_of_blocks": int(args.hbm_gib * 2048)} if args.hbm_gib > 0 else {}   # 512 KiB blocks
+    batch = args.batch if args.batch >= 0 else (16 if bf16 else 0)
+    if batch > 1:
+        hbm["batch_bodies"] = batch
+        if not args.window:
+            args.window = 3 * batch   # one batch on the GPU, one being staged, one retiring
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0, **hbm)
     mats, bufs = [], []
     for seed, mtype in zip((1789, 1805, 1901), mtypes):
@@ -486,7 +494,7 @@ def main():
                                 "(BASELINE configs[2] shape; %s)" % (N, NB, P, Q, world,
                                                                     "strong scaling, N fixed" if args.strong else
                                                                     "weak scaling from N=%d" % args.n)),
-                   "tasks_per_step": (N // NB) ** 3, "host_cores": os.cpu_count(), "replicas_diagnostic": bool(args.replicas),
+                   "tasks_per_step": (N // NB) ** 3, "batch_bodies": batch, "window": args.window, "host_cores": os.cpu_count(), "replicas_diagnostic": bool(args.replicas),
                    "l2": "inputs (%.1f GiB) far larger than L2" % (N * N * (8 if bf16 else 24) / 2 ** 30),
                    "parallelism": "1 process per GPU, %dx%d grid; %s exec streams in use per GPU" % (
                        P, Q, prof["resident_launches"] if prof else "?"),

@@ -175,6 +175,11 @@ typedef struct pb2_device_params_s {
     int use_priorities;           /* 1: the pending list hands out the task with the highest priority first (oldest first
                                      among equals), as the reference's priority-ordered lists do (PARSEC_GPU_USE_PRIORITIES,
                                      device_cuda_module.c:1683-1692); 0 (default): first come, first served */
+    int batch_bodies;             /* > 1: the manager gathers up to this many ready tasks, stages them in, and runs their
+                                     bodies back to back on one exec stream between parsec_b200_batch_begin and _end, so
+                                     that bodies calling the library's bf16 / tf32 GEMM share one grouped launch; every task
+                                     keeps its own completion event and stage-out.  0 (default): one task at a time, spread
+                                     over the exec streams (what the FP64 kernel wants) */
 } pb2_device_params_t;
 void pb2_device_params_default(pb2_device_params_t* p);
 /* The reference's MCA parameter names, as they reach a process in its environment (PARSEC_MCA_<name>,
@@ -229,6 +234,7 @@ typedef struct pb2_device_stats_s {
     uint64_t hbm_bytes_total, hbm_bytes_in_use;
     uint64_t host_submit_ns, host_retire_ns; /* manager-thread time spent submitting / retiring tasks */
     uint64_t nb_cleanouts;                   /* tasks whose stage-in was taken back (parsec_cuda_kernel_cleanout) */
+    uint64_t nb_batches;                     /* batched submissions (params.batch_bodies > 1) */
     uint64_t data_in_from_device[PB2_MAX_DEVICES]; /* bytes staged in, by source device (parsec_device_module_t.data_in_from_device,
                                                 device.h:130): [0] = host, [i >= 2] = the peer GPU with that device index */
 } pb2_device_stats_t;

@@ -61,6 +61,8 @@ struct TaskState {  // module-private part of a task in flight (pb2_gpu_task_t.r
     pb2_copy_t* d2d_src[PB2_MAX_PARAM_COUNT] = {nullptr};
     uint8_t d2d_demote[PB2_MAX_PARAM_COUNT] = {0};  // the source gave its ownership away: invalidate it when unpinned
     bool host_source_only = false;  // no D2D source (a pin that outlives this record could not hand the reader back)
+    uint64_t need_seq = 0;                // newest h2d event the body has to wait for
+    std::vector<cudaEvent_t> extra_waits; // events of other streams (NCCL) that make inputs valid
 };
 
 struct InFlight {
@@ -154,6 +156,7 @@ extern "C" void pb2_device_params_default(pb2_device_params_t* p) {
     p->sort_pending_tasks = 0;
     p->prefetch_deferred = 0;
     p->use_priorities = 0;
+    p->batch_bodies = 0;
 }
 
 // The reference's MCA parameters reach a process as environment variables PARSEC_MCA_<name> (parsec/utils/mca_param.c;
@@ -917,17 +920,17 @@ static void complete_w2r(pb2_device_s* d, TaskState* st) {
 // PB2_HOOK_RETURN_DISABLE when a CUDA call failed (the device is unusable), any other negative value is the task's own
 // (its body declined or a flow could not be staged) and leaves the device healthy.  In every negative case what
 // stage-in did has been taken back (cleanout_task) and t->reserved[0] is clear.
-static int try_submit_inner(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
+// Phase 1: stage every flow in and book the push completion.  The events the body will have to wait for are left in
+// st->need_seq / st->extra_waits.
+static int submit_stage_in(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     bool issued = false;
-    uint64_t need_seq = 0;
-    std::vector<cudaEvent_t> extra_waits;
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(t->flow_access[i] & PB2_FLOW_ACCESS_RW) || !t->flow_data[i]) continue;
         int rc = stage_in_flow(d, t, st, i, &issued);
         if (rc < 0) return rc;
         pb2_copy_t* c = t->flow_data[i]->device_copies[d->device_index];
-        need_seq = std::max(need_seq, c->ready_seq);
-        if (c->ready_event) extra_waits.push_back(c->ready_event);
+        st->need_seq = std::max(st->need_seq, c->ready_seq);
+        if (c->ready_event) st->extra_waits.push_back(c->ready_event);
     }
     if (issued) {
         const uint64_t seq = d->h2d_seq.load() + 1;
@@ -936,41 +939,50 @@ static int try_submit_inner(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     }
     for (int i = 0; i < t->nb_flows; ++i)
         if (st->pushed_mask & (1u << i)) complete_push_flow(d, t, i);
+    return 0;
+}
 
-    cudaStream_t last = d->h2d;
-    if (t->task_type == 0 && t->submit) {
-        // How many exec streams to spread over: a tile kernel has about one CTA per 128 KiB of its written tile
-        // (128x128 fp64 or 128x256 fp32), and a B200 wants ~2 x 148 CTAs queued.  An NB=1024 fp64 task (64 CTAs) uses 5
-        // streams, an NB=512 one (16 CTAs) all 16, an NB=2048 one (256 CTAs) the minimum of 4.
-        size_t wbytes = 0;
-        for (int i = 0; i < t->nb_flows; ++i)
-            if (t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) wbytes = std::max<size_t>(wbytes, t->flow_nb_elts[i]);
-        const int ctas = (int)std::max<size_t>(1, wbytes >> 17);
-        const int active = std::min<int>((int)d->exec.size(), std::max(4, (2 * 148 + ctas - 1) / ctas));
-        d->active_exec = active;
-        int s = d->next_exec % active;
-        d->next_exec = (d->next_exec + 1) % active;
-        st->exec_stream = s;
-        if (need_seq > d->exec_waited_seq[s]) {
-            // waiting on a newer event of the same in-order stream covers every older one; if the ring has
-            // wrapped past need_seq the slot holds a later event, which is still sufficient
-            const uint64_t now = d->h2d_seq.load();
-            uint64_t w = (now - need_seq >= (uint64_t)EVENT_RING) ? now : need_seq;
-            PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], d->h2d_events[w % EVENT_RING], 0));
-            d->exec_waited_seq[s] = w;
-        }
-        for (cudaEvent_t e : extra_waits) PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], e, 0));
-        int rc = t->submit(d, t, d->exec[s]);
-        if (rc != PB2_HOOK_RETURN_DONE) return rc < 0 && rc != PB2_HOOK_RETURN_DISABLE ? rc : PB2_HOOK_RETURN_ERROR;
-        d->stats.kernel_launches++;
-        if (d->params.profile_launches && d->launch_marks[s].size() < 16384) {
-            cudaEvent_t mark = nullptr;
-            if (cudaEventCreate(&mark) == cudaSuccess && cudaEventRecord(mark, d->exec[s]) == cudaSuccess)
-                d->launch_marks[s].push_back(mark);
-        }
-        last = d->exec[s];
+// How many exec streams to spread over: a tile kernel has about one CTA per 128 KiB of its written tile
+// (128x128 fp64 or 128x256 fp32), and a B200 wants ~2 x 148 CTAs queued.  An NB=1024 fp64 task (64 CTAs) uses 5
+// streams, an NB=512 one (16 CTAs) all 16, an NB=2048 one (256 CTAs) the minimum of 4.
+static int pick_exec_stream(pb2_device_s* d, const pb2_gpu_task_t* t) {
+    size_t wbytes = 0;
+    for (int i = 0; i < t->nb_flows; ++i)
+        if (t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) wbytes = std::max<size_t>(wbytes, t->flow_nb_elts[i]);
+    const int ctas = (int)std::max<size_t>(1, wbytes >> 17);
+    const int active = std::min<int>((int)d->exec.size(), std::max(4, (2 * 148 + ctas - 1) / ctas));
+    d->active_exec = active;
+    const int s = d->next_exec % active;
+    d->next_exec = (d->next_exec + 1) % active;
+    return s;
+}
+
+// Phase 2: make exec stream s wait for the task's inputs and run its body there.
+static int submit_body(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int s) {
+    st->exec_stream = s;
+    if (st->need_seq > d->exec_waited_seq[s]) {
+        // waiting on a newer event of the same in-order stream covers every older one; if the ring has
+        // wrapped past need_seq the slot holds a later event, which is still sufficient
+        const uint64_t now = d->h2d_seq.load();
+        uint64_t w = (now - st->need_seq >= (uint64_t)EVENT_RING) ? now : st->need_seq;
+        PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], d->h2d_events[w % EVENT_RING], 0));
+        d->exec_waited_seq[s] = w;
     }
-    // stage-out is enqueued now, ordered after the kernel by an event (a8)
+    for (cudaEvent_t e : st->extra_waits) PB2_DEV_TRY(d, cudaStreamWaitEvent(d->exec[s], e, 0));
+    int rc = t->submit(d, t, d->exec[s]);
+    if (rc != PB2_HOOK_RETURN_DONE) return rc < 0 && rc != PB2_HOOK_RETURN_DISABLE ? rc : PB2_HOOK_RETURN_ERROR;
+    d->stats.kernel_launches++;
+    return 0;
+}
+
+// Phase 3: the task's completion event, after its stage-out (a8) when it has one; file it as in flight.
+static int submit_finish(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
+    cudaStream_t last = st->exec_stream >= 0 ? d->exec[st->exec_stream] : d->h2d;
+    if (st->exec_stream >= 0 && d->params.profile_launches && d->launch_marks[st->exec_stream].size() < 16384) {
+        cudaEvent_t mark = nullptr;
+        if (cudaEventCreate(&mark) == cudaSuccess && cudaEventRecord(mark, last) == cudaSuccess)
+            d->launch_marks[st->exec_stream].push_back(mark);
+    }
     uint32_t out_mask = 0;
     for (int i = 0; i < t->nb_flows; ++i)
         if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && (t->pushout & (1 << i))) out_mask |= 1u << i;
@@ -997,20 +1009,70 @@ static int try_submit_inner(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     return 0;
 }
 
+static void abandon_submission(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int rc) {
+    // if the body was already launched the kernel may be running: let the streams drain before the tiles go back
+    if (rc == PB2_HOOK_RETURN_DISABLE) cudaDeviceSynchronize();
+    cleanout_task(d, t, st);
+    if (st->done) d->event_pool.push_back(st->done);
+    delete st;
+    t->reserved[0] = nullptr;
+}
+
 static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
     int r = reserve_device_space(d, t);
     if (r != 0) return 1;
     TaskState* st = new TaskState();
     t->reserved[0] = st;
-    int rc = try_submit_inner(d, t, st);
-    if (rc < 0) {
-        // if the body was already launched the kernel may be running: let the streams drain before the tiles go back
-        if (rc == PB2_HOOK_RETURN_DISABLE) cudaDeviceSynchronize();
-        cleanout_task(d, t, st);
-        if (st->done) d->event_pool.push_back(st->done);
-        delete st;
-        t->reserved[0] = nullptr;
+    int rc = submit_stage_in(d, t, st);
+    if (rc == 0 && t->task_type == 0 && t->submit) rc = submit_body(d, t, st, pick_exec_stream(d, t));
+    if (rc == 0) rc = submit_finish(d, t, st);
+    if (rc < 0) abandon_submission(d, t, st, rc);
+    return rc;
+}
+
+// The second half of a batched submission (params.batch_bodies > 1): the tasks of `batch` have been reserved and
+// staged in (try_stage); their bodies now run back to back on ONE exec stream between parsec_b200_batch_begin and
+// _end, so that bodies which call the library's batchable kernels end up in one grouped launch.  Every task still
+// gets its own completion event (they all fire when the stream reaches the end of the batch) and its own stage-out.
+// Tasks whose body declines are taken back one by one; `failed` receives (task, status) for the caller to complete.
+extern "C" int parsec_b200_batch_begin(void* stream);
+extern "C" int parsec_b200_batch_end(void* stream);
+static void submit_batch(pb2_device_s* d, std::vector<pb2_gpu_task_t*>& batch,
+                         std::vector<std::pair<pb2_gpu_task_t*, int>>& failed) {
+    if (batch.empty()) return;
+    const int s = pick_exec_stream(d, batch.front());
+    std::vector<pb2_gpu_task_t*> ran;
+    const bool bracket = parsec_b200_batch_begin(d->exec[s]) == PB2_SUCCESS;
+    for (pb2_gpu_task_t* t : batch) {
+        TaskState* st = (TaskState*)t->reserved[0];
+        int rc = (t->task_type == 0 && t->submit) ? submit_body(d, t, st, s) : 0;
+        if (rc < 0) {
+            abandon_submission(d, t, st, rc);
+            failed.push_back({t, rc});
+        } else {
+            ran.push_back(t);
+        }
     }
+    if (bracket && parsec_b200_batch_end(d->exec[s]) != PB2_SUCCESS) d->failed = true;
+    for (pb2_gpu_task_t* t : ran) {
+        TaskState* st = (TaskState*)t->reserved[0];
+        int rc = d->failed ? PB2_HOOK_RETURN_DISABLE : submit_finish(d, t, st);
+        if (rc < 0) {
+            abandon_submission(d, t, st, rc);
+            failed.push_back({t, rc});
+        }
+    }
+    batch.clear();
+}
+
+// first half: 0 = staged and waiting in the batch, 1 = stalled, < 0 = does not run here (already taken back)
+static int try_stage(pb2_device_s* d, pb2_gpu_task_t* t) {
+    int r = reserve_device_space(d, t);
+    if (r != 0) return 1;
+    TaskState* st = new TaskState();
+    t->reserved[0] = st;
+    int rc = submit_stage_in(d, t, st);
+    if (rc < 0) abandon_submission(d, t, st, rc);
     return rc;
 }
 
@@ -1212,12 +1274,46 @@ static int manager_loop(pb2_device_s* d, pb2_gpu_task_t* task) {
         }
         if (cur) {
             auto ts0 = std::chrono::steady_clock::now();
-            int r = try_submit(d, cur);
+            int r;
+            if (d->params.batch_bodies > 1) {
+                // gather what is ready now, up to batch_bodies tasks: stage each in, then run their bodies as one batch
+                std::vector<pb2_gpu_task_t*> batch;
+                std::vector<std::pair<pb2_gpu_task_t*, int>> declined;
+                r = try_stage(d, cur);
+                while (r == 0) {
+                    batch.push_back(cur);
+                    cur = nullptr;
+                    if ((int)batch.size() >= d->params.batch_bodies || d->inflight_count + batch.size() >= max_inflight) break;
+                    if (!d->stalled.empty()) {
+                        cur = d->stalled.front();
+                        d->stalled.pop_front();
+                    } else {
+                        std::lock_guard<std::mutex> g(d->pending_lock);
+                        cur = pop_pending(d);
+                    }
+                    if (!cur) break;
+                    r = try_stage(d, cur);
+                }
+                const size_t launched = batch.size();
+                submit_batch(d, batch, declined);
+                d->stats.nb_batches += launched ? 1 : 0;
+                bool left = false;
+                for (auto& f : declined) {
+                    if (f.first->complete) f.first->complete(f.first, f.second, f.first->complete_cookie);
+                    free(f.first);
+                    if (d->mutex.fetch_sub(1) == 1) left = true;
+                }
+                if (left) return leave();
+                if (!cur) r = 0;  // everything gathered is in flight
+            } else {
+                r = try_submit(d, cur);
+            }
             d->stats.host_submit_ns +=
                 (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - ts0).count();
             if (r == 0) {
                 progressed = true;
                 cur = nullptr;
+                if (d->params.batch_bodies > 1) burst = 8;  // a batch is a burst
                 // keep feeding the streams: poll completions only every few submissions (each poll is one
                 // cudaEventQuery per stream), a submission is what keeps the copy engines and SMs busy
                 if (++burst < 8) continue;

@@ -999,8 +999,9 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
     int c_tma = (!epi_direct && !(((uintptr_t)C) & 15) && !(ldc & 3)) ? 1 : 0;
     if (c_tma && umma_tmap(&mc, C, m, n, ldc, 3, 4)) return PB2_ERR_CUDA;
     if (!c_tma) memset(&mc, 0, sizeof(mc));
-    if (ctas == 5 && (k == 0 || !c_tma)) ctas = 3;  // nothing to multiply, or a C that TMA cannot address: per-tile kernel
-    if (ctas == 5) {
+    int mode = ctas;
+    if (mode == 5 && (k == 0 || !c_tma)) mode = 3;  // nothing to multiply, or a C that TMA cannot address: per-tile kernel
+    if (mode == 5) {
         UmmaTask t;
         memset(&t, 0, sizeof(t));
         t.mapA = ma; t.mapBh = mb; t.mapC = mc;
@@ -1017,10 +1018,16 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
             }
             return PB2_SUCCESS;
         }
-        std::vector<UmmaTask> one(1, t);
-        return launch_group<EB>(one, (cudaStream_t)stream);
+        // A single call with no more tiles than CTA pairs gains nothing from the persistent walk (one tile per pair, one
+        // CTA per SM) and loses the co-residency of two per-tile CTAs per SM that lets launches on other streams overlap
+        // (measured: a stream of unbatched 2048^3 tasks on 4 streams 1130 -> 638 TFLOP/s): it takes the per-tile kernel.
+        if (t.pairs_m * t.tiles_n > 74) {
+            std::vector<UmmaTask> one(1, t);
+            return launch_group<EB>(one, (cudaStream_t)stream);
+        }
+        mode = 3;
     }
-    if (ctas >= 3) {
+    if (mode >= 3) {
         static bool pair_attr_set[64] = {false};
         if (dev < 64 && !pair_attr_set[dev]) {
             if (cudaFuncSetAttribute(gemm_umma_pair<P_STAGES_2CTA, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1031,7 +1038,7 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
             pair_attr_set[dev] = true;
         }
         dim3 pgrid(2 * ((m + 2 * G_BM - 1) / (2 * G_BM)) * ((n + G_BN - 1) / G_BN));
-        if (ctas == 3)
+        if (mode == 3)
             gemm_umma_pair<P_STAGES_2CTA, EB><<<pgrid, G_THREADS, pair_smem(P_STAGES_2CTA), (cudaStream_t)stream>>>(
                 ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
         else
@@ -1040,7 +1047,7 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
         return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
     }
     dim3 grid(((m + G_BM - 1) / G_BM) * ((n + G_BN - 1) / G_BN));
-    if (ctas == 1)
+    if (mode == 1)
         gemm_bf16_tcgen05<G_STAGES_1CTA, EB><<<grid, G_THREADS, gemm_smem(G_STAGES_1CTA), (cudaStream_t)stream>>>(
             ma, mb, m, n, k, alpha, beta, C, ldc, mc, c_tma);
     else

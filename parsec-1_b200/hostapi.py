@@ -27,14 +27,15 @@ class DeviceParams(C.Structure):
                 ("memory_number_of_blocks", C.c_int64), ("max_streams", C.c_int),
                 ("max_number_of_ejected_data", C.c_int), ("max_inflight_tasks", C.c_int), ("trace_events", C.c_int),
                 ("profile_launches", C.c_int), ("sort_pending_tasks", C.c_int),
-                ("prefetch_deferred", C.c_int), ("use_priorities", C.c_int)]
+                ("prefetch_deferred", C.c_int), ("use_priorities", C.c_int),
+                ("batch_bodies", C.c_int)]
 
 
 class DeviceStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "executed_tasks data_in_from_host data_in_from_peers data_out_to_host required_data_in required_data_out "
         "nb_data_faults nb_evictions nb_w2r_tasks nb_w2r_tiles nb_stalls kernel_launches hbm_bytes_total "
-        "hbm_bytes_in_use host_submit_ns host_retire_ns nb_cleanouts").split()] + [("data_in_from_device", C.c_uint64 * 10)]
+        "hbm_bytes_in_use host_submit_ns host_retire_ns nb_cleanouts nb_batches").split()] + [("data_in_from_device", C.c_uint64 * 10)]
 
     def as_dict(self):
         d = {n: int(getattr(self, n)) for n, _ in self._fields_[:-1]}

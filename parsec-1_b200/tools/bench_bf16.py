@@ -69,3 +69,21 @@ for S in (1, 2, 4):
         e1.synchronize()
         best = min(best, e0.elapsed_time(e1))
     print("tile stream S=%d: %d x 2048^3 (beta=1) in %.3f ms -> %.1f TFLOP/s" % (S, ntile * 4, best, 2 * nb ** 3 * ntile * 4 / best * 1e-9))
+
+# the same stream of tile tasks, handed over in batches (parsec_b200_batch_begin / _end): one grouped launch per batch
+L.parsec_b200_batch_begin.argtypes = [H.C.c_void_p]
+L.parsec_b200_batch_end.argtypes = [H.C.c_void_p]
+for batch in (4, 8, 16):
+    st = torch.cuda.current_stream().cuda_stream
+
+    def run_batched():
+        for i0 in range(0, ntile * 4, batch):
+            L.parsec_b200_batch_begin(st)
+            for i in range(i0, min(i0 + batch, ntile * 4)):
+                t = i % ntile
+                L.parsec_b200_gemm_bf16_sm100(b"N", b"N", nb, nb, nb, 1.0, As[t].data_ptr(), nb, Bs[t].data_ptr(), nb, 1.0,
+                                              Cs[t].data_ptr(), nb, st)
+            L.parsec_b200_batch_end(st)
+    best = timed(run_batched, 1)
+    print("tile stream, batches of %2d: %d x 2048^3 (beta=1) in %.3f ms -> %.1f TFLOP/s" % (
+        batch, ntile * 4, best, 2 * nb ** 3 * ntile * 4 / best * 1e-9))
