@@ -314,7 +314,7 @@ def main():
                     "many exec streams as its tile size needs: 5 at NB=1024, 16 at NB=512)")
     ap.add_argument("--batch", type=int, default=-1,
                     help="tasks per batched submission (one grouped tcgen05 launch per batch); -1 = 16 for --dtype bf16, "
-                         "off for f64 (the DMMA kernel fills the GPU through stream concurrency instead)")
+                         "32 for f64 tiles of 512 and below, off for larger f64 tiles")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the extra checked step after the timed regions")
     ap.add_argument("--hbm-gib", type=float, default=0.0,
@@ -381,10 +381,12 @@ def main():
             peak_tf = live_tf
             peak_src = "measured live: torch.matmul fp64 8192^3 (cuBLAS), best of 10 (profiles/fp64_peak_r2.json missing)"
     hbm = {"memory_number_of_blocks": int(args.hbm_gib * 2048)} if args.hbm_gib > 0 else {}   # 512 KiB blocks
-    batch = args.batch if args.batch >= 0 else (16 if bf16 else 0)
+    # tensor-core tile tasks share grouped launches; FP64 tiles of 512 and below are launch bound one by one (a 256^3
+    # task is 4 CTAs), larger ones fill the GPU through stream concurrency
+    batch = args.batch if args.batch >= 0 else (16 if bf16 else (32 if NB <= 512 else 0))
     if batch > 1:
         hbm["batch_bodies"] = batch
-        if not args.window:
+        if bf16 and not args.window:
             args.window = 3 * batch   # one batch on the GPU, one being staged, one retiring
     dev = H.Device(local_rank, max_inflight_tasks=args.inflight, max_streams=args.streams, profile_launches=0, **hbm)
     mats, bufs = [], []

@@ -81,9 +81,10 @@ int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, f
 int parsec_b200_gemm_tf32_sm100(char transa, char transb, int m, int n, int k, float alpha, const float* A, int lda,
                                 const float* B, int ldb, float beta, float* C, int ldc, void* stream);
 
-/* Batches.  The bf16 / tf32 GEMM calls one thread makes on `stream` between parsec_b200_batch_begin and
- * parsec_b200_batch_end are recorded and launched together as one grouped persistent kernel (at _end, or every 16
- * calls): the tile tasks a task runtime has ready at the same time share one launch, whose CTA pairs walk the output
+/* Batches.  The GEMM calls one thread makes on `stream` between parsec_b200_batch_begin and parsec_b200_batch_end are
+ * recorded and launched together: the bf16 / tf32 ones as one grouped persistent tcgen05 kernel (at _end, or every 16
+ * calls), the fp64 ones (untransposed, aligned operands) as one grid holding the tiles of all of them (at _end, or
+ * every 64 calls; a 256^3 fp64 tile task is four CTAs and costs the host more to launch than the GPU to run): the tile tasks a task runtime has ready at the same time share one launch, whose CTA pairs walk the output
  * tiles of all of them with the epilogue of one tile under the MMAs of the next.  The reference has no counterpart
  * (its bodies launch one cuBLAS call per task, nvlink.jdf:142); the device module brackets the bodies it submits
  * together with these calls, so bodies need no change.  Results are those of the single calls. */

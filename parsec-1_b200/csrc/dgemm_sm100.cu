@@ -201,9 +201,12 @@ __device__ __forceinline__ void dmma884p(double& d0, double& d1, double a, doubl
         : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(T_THREADS, 1)
-dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
-             double alpha, double beta, double* __restrict__ C, int ldc) {
+// One 128 x 128 tile of C = alpha A B + beta C; `tile` is its index among the tiles of this GEMM (column-major over
+// tiles).  Shared by the one-GEMM kernel and the grouped one.
+__device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const CUtensorMap* mapB_p, int M, int N, int K,
+                                               double alpha, double beta, double* __restrict__ C, int ldc, int tile) {
+    const CUtensorMap& mapA = *mapA_p;
+    const CUtensorMap& mapB = *mapB_p;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t sbase0 = (raw + 1023u) & ~1023u;
@@ -213,7 +216,7 @@ dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ C
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tiles_m = (M + BM - 1) / BM;
-    const int bm = blockIdx.x % tiles_m, bn = blockIdx.x / tiles_m;
+    const int bm = tile % tiles_m, bn = tile / tiles_m;
     const int m0 = bm * BM, n0 = bn * BN;
     const int KT = (K + BK - 1) / BK;
 
@@ -409,6 +412,39 @@ dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ C
     }
 }
 
+__global__ void __launch_bounds__(T_THREADS, 1)
+dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
+             double alpha, double beta, double* __restrict__ C, int ldc) {
+    dgemm_tile_tma(&mapA, &mapB, M, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
+}
+
+// Grouped launch: the tiles of several independent GEMMs (the tile tasks a task runtime has ready together) in ONE
+// grid.  A 256 x 256 fp64 tile task is four CTAs and about a microsecond of tensor-core time; launched one by one such
+// tasks cost the host more than the GPU (6.5 us of manager time per task against 1 us of work).  Here CTA b finds its
+// GEMM by tile_begin and runs the same tile code; tensor maps travel in the kernel parameter space.
+constexpr int DG_MAX_GROUP = 64;
+struct DgemmTask {
+    CUtensorMap mapA, mapB;
+    double* C;
+    double alpha, beta;
+    int M, N, K, ldc;
+    int tile_begin, pad_;
+};
+template <int MAXT>
+struct DgemmGroup {
+    DgemmTask t[MAXT];
+    int ntasks;
+};
+template <int MAXT>
+__global__ void __launch_bounds__(T_THREADS, 1) dgemm_nn_tma_grouped(const __grid_constant__ DgemmGroup<MAXT> g) {
+    int t = 0;
+    const int b = (int)blockIdx.x;
+#pragma unroll 1
+    while (t + 1 < g.ntasks && b >= g.t[t + 1].tile_begin) ++t;
+    const DgemmTask& k = g.t[t];
+    dgemm_tile_tma(&k.mapA, &k.mapB, k.M, k.N, k.K, k.alpha, k.beta, k.C, k.ldc, b - k.tile_begin);
+}
+
 // ---------------------------------------------------------------------------------------------
 // General kernel: any M, N, K, any transposes, any alignment.  CTA tile 64x64, BK = 16,
 // 128 threads = 4 warps (2x2), warp tile 32x32 = 4x4 DMMA tiles, predicated scalar staging.
@@ -494,6 +530,10 @@ static int ensure_smem_attr() {
     if (e != cudaSuccess) return PB2_ERR_CUDA;
     e = cudaFuncSetAttribute(dgemm_nn_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
+    e = cudaFuncSetAttribute(dgemm_nn_tma_grouped<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e != cudaSuccess) return PB2_ERR_CUDA;
+    e = cudaFuncSetAttribute(dgemm_nn_tma_grouped<DG_MAX_GROUP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e != cudaSuccess) return PB2_ERR_CUDA;
     if (dev < 64) g_attr_set[dev] = true;
     return PB2_SUCCESS;
 }
@@ -543,6 +583,50 @@ static int get_tmap(CUtensorMap* out, const void* p, int d0, int d1, int ld, int
     return 0;
 }
 
+// ---- batches (parsec_b200_batch_begin / _end, gemm_tcgen05.cu): DGEMM calls recorded on one stream by one thread
+struct DgemmBatch {
+    bool open = false;
+    void* stream = nullptr;
+    int status = PB2_SUCCESS;
+    std::vector<DgemmTask> tasks;
+};
+static thread_local DgemmBatch g_dbatch;
+
+static int dgemm_batch_launch(std::vector<DgemmTask>& tasks, cudaStream_t st) {
+    if (tasks.empty()) return PB2_SUCCESS;
+    int total = 0;
+    for (DgemmTask& t : tasks) {
+        t.tile_begin = total;
+        total += ((t.M + BM - 1) / BM) * ((t.N + BN - 1) / BN);
+    }
+    const int n = (int)tasks.size();
+    if (n <= 8) {
+        DgemmGroup<8> g;
+        memcpy(g.t, tasks.data(), sizeof(DgemmTask) * (size_t)n);
+        g.ntasks = n;
+        dgemm_nn_tma_grouped<8><<<dim3(total), T_THREADS, T_SMEM, st>>>(g);
+    } else {
+        DgemmGroup<DG_MAX_GROUP> g;
+        memcpy(g.t, tasks.data(), sizeof(DgemmTask) * (size_t)n);
+        g.ntasks = n;
+        dgemm_nn_tma_grouped<DG_MAX_GROUP><<<dim3(total), T_THREADS, T_SMEM, st>>>(g);
+    }
+    tasks.clear();
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+void dgemm_batch_open(void* stream) {
+    g_dbatch.open = true;
+    g_dbatch.stream = stream;
+    g_dbatch.status = PB2_SUCCESS;
+}
+int dgemm_batch_close(void* stream) {
+    if (!g_dbatch.open || g_dbatch.stream != stream) return PB2_SUCCESS;
+    g_dbatch.open = false;
+    int rc = dgemm_batch_launch(g_dbatch.tasks, (cudaStream_t)stream);
+    return g_dbatch.status != PB2_SUCCESS ? g_dbatch.status : rc;
+}
+
 static inline int trans_of(char c) {
     if (c == 'N' || c == 'n') return 0;
     if (c == 'T' || c == 't' || c == 'C' || c == 'c') return 1;
@@ -569,6 +653,18 @@ extern "C" int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, i
         if (rc != PB2_SUCCESS) return rc;
         CUtensorMap ma, mb;
         if (get_tmap(&ma, A, m, k, lda, 0) || get_tmap(&mb, B, k, n, ldb, 1)) return PB2_ERR_CUDA;
+        if (g_dbatch.open && g_dbatch.stream == stream) {  // recorded; launched with the rest of the batch
+            DgemmTask t;
+            memset(&t, 0, sizeof(t));
+            t.mapA = ma; t.mapB = mb; t.C = C; t.alpha = alpha; t.beta = beta; t.M = m; t.N = n; t.K = k; t.ldc = ldc;
+            g_dbatch.tasks.push_back(t);
+            if ((int)g_dbatch.tasks.size() == DG_MAX_GROUP) {
+                rc = dgemm_batch_launch(g_dbatch.tasks, st);
+                if (rc != PB2_SUCCESS) g_dbatch.status = rc;
+                return rc;
+            }
+            return PB2_SUCCESS;
+        }
         dim3 grid(((m + BM - 1) / BM) * ((n + BN - 1) / BN));
         dgemm_nn_tma<<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
     } else if (!ta && !tb && aligned && k > 0 && m % BM == 0 && n % BN == 0 && k % BK == 0) {

@@ -1059,11 +1059,16 @@ static int launch_umma_gemm(char transa, char transb, int m, int n, int k, float
 }  // namespace pb2
 
 // Batches: the tile GEMMs a caller has ready at the same time go to the GPU as ONE grouped launch.  Between
-// parsec_b200_batch_begin(stream) and parsec_b200_batch_end(stream) the bf16 / tf32 GEMM calls this thread makes on
-// `stream` are only recorded; _end (or the 16th call) launches them.  The device module brackets the bodies of the
+// parsec_b200_batch_begin(stream) and parsec_b200_batch_end(stream) the bf16 / tf32 / fp64 GEMM calls this thread makes
+// on `stream` are only recorded; _end (or the 16th tensor-core call, the 64th FP64 call) launches them.  The device module brackets the bodies of the
 // tasks it submits together with these two calls, so a JDF body that calls parsec_b200_gemm_bf16 needs no change.
+namespace pb2 {
+void dgemm_batch_open(void* stream);   // dgemm_sm100.cu: the FP64 kernel's share of a batch
+int dgemm_batch_close(void* stream);
+}
 extern "C" int parsec_b200_batch_begin(void* stream) {
     if (pb2::g_batch.open) return PB2_ERR_EXISTS;
+    pb2::dgemm_batch_open(stream);
     pb2::g_batch.open = true;
     pb2::g_batch.stream = stream;
     pb2::g_batch.status = PB2_SUCCESS;
@@ -1075,7 +1080,8 @@ extern "C" int parsec_b200_batch_end(void* stream) {
     int rc = pb2::g_batch.status;
     int r1 = pb2::launch_group<2>(pb2::g_batch.bf16, (cudaStream_t)stream);
     int r2 = pb2::launch_group<4>(pb2::g_batch.tf32, (cudaStream_t)stream);
-    return rc != PB2_SUCCESS ? rc : r1 != PB2_SUCCESS ? r1 : r2;
+    int r3 = pb2::dgemm_batch_close(stream);
+    return rc != PB2_SUCCESS ? rc : r1 != PB2_SUCCESS ? r1 : r2 != PB2_SUCCESS ? r2 : r3;
 }
 
 extern "C" int parsec_b200_gemm_bf16_sm100(char transa, char transb, int m, int n, int k, float alpha, const void* A,

@@ -106,3 +106,42 @@ def test_linearity_at_full_tile_size():
     torch.cuda.synchronize()
     err = (outs[0] + outs[1] - outs[2]).abs().max().item()
     assert err < 1e-11
+
+
+def test_batched_dgemm_calls_give_the_results_of_single_calls():
+    """parsec_b200_batch_begin / _end around 70 fp64 tile GEMMs of mixed shapes (one grouped grid of 64 + one of 6):
+    bit-identical to the same calls made one by one; a transposed call inside the batch is launched on its own."""
+    import torch
+    L = H.lib()
+    L.parsec_b200_batch_begin.argtypes = [H.C.c_void_p]
+    L.parsec_b200_batch_end.argtypes = [H.C.c_void_p]
+    shapes = [(256, 256, 256), (128, 384, 64), (200, 136, 72), (512, 256, 1024), (1000, 24, 16), (256, 256, 256), (130, 130, 130)] * 10
+    g = torch.Generator(device="cuda")
+    g.manual_seed(5)
+    ops = []
+    for i, (m, n, k) in enumerate(shapes):
+        A = torch.rand(k, m, device="cuda", generator=g, dtype=torch.float64) - 0.5      # column-major m x k
+        B = torch.rand(n, k, device="cuda", generator=g, dtype=torch.float64) - 0.5
+        Cm = torch.rand(n, m, device="cuda", generator=g, dtype=torch.float64) - 0.5
+        ops.append((m, n, k, 1.0 + 0.5 * (i % 2), float(i % 3) - 1.0, A, B, Cm))
+    s = torch.cuda.current_stream().cuda_stream
+
+    def run(batched):
+        outs = [op[7].clone() for op in ops]
+        if batched:
+            assert L.parsec_b200_batch_begin(s) == 0
+        for j, ((m, n, k, alpha, beta, A, B, _), Cm) in enumerate(zip(ops, outs)):
+            ta = b"T" if (j == 3 and m == k) else b"N"
+            assert L.parsec_b200_dgemm(ta, b"N", m, n, k, alpha, A.data_ptr(), m if ta == b"N" else k, B.data_ptr(), k, beta,
+                                       Cm.data_ptr(), m, s) == 0
+        if batched:
+            assert L.parsec_b200_batch_end(s) == 0
+        torch.cuda.synchronize()
+        return outs
+
+    single, batched = run(False), run(True)
+    for a, b, op in zip(single, batched, ops):
+        assert torch.equal(a, b), op[:3]
+    m, n, k, alpha, beta, A, B, Cm = ops[0]
+    want = beta * Cm + alpha * (B @ A)
+    assert (single[0] - want).abs().max().item() < 1e-12
