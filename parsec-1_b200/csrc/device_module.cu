@@ -63,6 +63,20 @@ struct TaskState {  // module-private part of a task in flight (pb2_gpu_task_t.r
     bool host_source_only = false;  // no D2D source (a pin that outlives this record could not hand the reader back)
     uint64_t need_seq = 0;                // newest h2d event the body has to wait for
     std::vector<cudaEvent_t> extra_waits; // events of other streams (NCCL) that make inputs valid
+    bool done_shared = false;             // `done` belongs to a later task of the same batch (it gives it back)
+    void reset() {                        // back to the state of a fresh record, keeping the vectors' storage
+        done = nullptr;
+        exec_stream = -1;
+        is_w2r = false;
+        w2r_copies.clear();
+        pushed_mask = staged_mask = 0;
+        memset(d2d_src, 0, sizeof(d2d_src));
+        memset(d2d_demote, 0, sizeof(d2d_demote));
+        host_source_only = false;
+        need_seq = 0;
+        extra_waits.clear();
+        done_shared = false;
+    }
 };
 
 struct InFlight {
@@ -133,6 +147,7 @@ struct pb2_device_s {
     std::unordered_map<void*, size_t> registered;
     pb2_device_hooks_t hooks = {nullptr, nullptr};
     std::unordered_set<pb2_copy_t*> all_copies;  // every device copy this module has created and not released yet
+    std::vector<pb2::TaskState*> state_pool;     // recycled per-task records (manager thread only)
     std::vector<std::vector<cudaEvent_t>> launch_marks;  // profile_launches: completion marks per exec stream
 };
 
@@ -205,6 +220,22 @@ static cudaEvent_t get_event(pb2_device_s* d) {
     cudaEvent_t e = nullptr;
     cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
     return e;
+}
+
+static TaskState* new_state(pb2_device_s* d) {
+    if (d->state_pool.empty()) return new TaskState();
+    TaskState* st = d->state_pool.back();
+    d->state_pool.pop_back();
+    return st;
+}
+static void free_state(pb2_device_s* d, TaskState* st) {
+    if (!st) return;
+    if (d->state_pool.size() >= 1024) {
+        delete st;
+        return;
+    }
+    st->reset();
+    d->state_pool.push_back(st);
 }
 
 static void trace(pb2_device_s* d, pb2_gpu_task_t* t, int f, int kind, int transfer) {
@@ -383,6 +414,8 @@ extern "C" int pb2_device_destroy(pb2_device_t* d) {
             if (f.st && f.st->is_w2r) complete_w2r(d, f.st);
             delete f.st;
         }
+    for (TaskState* st : d->state_pool) delete st;
+    d->state_pool.clear();
     for (pb2_gpu_task_t* t : d->deferred) free(t);
     drain_peer_unpins(d);
     // every copy, also the ones in no list (dropped from the LRU while they had readers, or chopped out for a writer)
@@ -829,7 +862,7 @@ static void cleanout_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
 
 // ------------------------------------------------------------------------------------ W2R (a11)
 static bool start_w2r(pb2_device_s* d) {
-    TaskState* st = new TaskState();
+    TaskState* st = new_state(d);
     st->is_w2r = true;
     int limit = std::max(1, d->params.max_number_of_ejected_data);
     for (pb2_copy_t* c = d->owned_lru.head; c && (int)st->w2r_copies.size() < limit;) {
@@ -855,7 +888,7 @@ static bool start_w2r(pb2_device_s* d) {
         c = next;
     }
     if (st->w2r_copies.empty()) {
-        delete st;
+        free_state(d, st);
         return false;
     }
     // the dirty bytes were produced on exec streams whose completion the host has already observed
@@ -976,7 +1009,9 @@ static int submit_body(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, int s)
 }
 
 // Phase 3: the task's completion event, after its stage-out (a8) when it has one; file it as in flight.
-static int submit_finish(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
+// `shared` (batches): an event already recorded at the end of the batch on the task's exec stream; a task without
+// stage-out takes it as its completion event instead of recording one of its own.
+static int submit_finish(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, cudaEvent_t shared = nullptr) {
     cudaStream_t last = st->exec_stream >= 0 ? d->exec[st->exec_stream] : d->h2d;
     if (st->exec_stream >= 0 && d->params.profile_launches && d->launch_marks[st->exec_stream].size() < 16384) {
         cudaEvent_t mark = nullptr;
@@ -986,6 +1021,13 @@ static int submit_finish(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     uint32_t out_mask = 0;
     for (int i = 0; i < t->nb_flows; ++i)
         if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && (t->pushout & (1 << i))) out_mask |= 1u << i;
+    if (shared && !out_mask) {
+        st->done = shared;
+        st->done_shared = true;
+        d->inflight_q[(size_t)st->exec_stream].push_back({t, st});
+        d->inflight_count++;
+        return 0;
+    }
     st->done = get_event(d);
     if (!st->done) {
         d->failed = true;
@@ -1013,15 +1055,15 @@ static void abandon_submission(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st
     // if the body was already launched the kernel may be running: let the streams drain before the tiles go back
     if (rc == PB2_HOOK_RETURN_DISABLE) cudaDeviceSynchronize();
     cleanout_task(d, t, st);
-    if (st->done) d->event_pool.push_back(st->done);
-    delete st;
+    if (st->done && !st->done_shared) d->event_pool.push_back(st->done);
+    free_state(d, st);
     t->reserved[0] = nullptr;
 }
 
 static int try_submit(pb2_device_s* d, pb2_gpu_task_t* t) {
     int r = reserve_device_space(d, t);
     if (r != 0) return 1;
-    TaskState* st = new TaskState();
+    TaskState* st = new_state(d);
     t->reserved[0] = st;
     int rc = submit_stage_in(d, t, st);
     if (rc == 0 && t->task_type == 0 && t->submit) rc = submit_body(d, t, st, pick_exec_stream(d, t));
@@ -1054,14 +1096,30 @@ static void submit_batch(pb2_device_s* d, std::vector<pb2_gpu_task_t*>& batch,
         }
     }
     if (bracket && parsec_b200_batch_end(d->exec[s]) != PB2_SUCCESS) d->failed = true;
+    // one completion event for the whole batch (the tasks end together, when the stream gets here); the last task that
+    // uses it owns it and, retiring last from the same in-order queue, gives it back
+    cudaEvent_t shared = nullptr;
+    if (!d->failed && ran.size() > 1 && !d->params.profile_launches) {
+        shared = get_event(d);
+        if (shared && cudaEventRecord(shared, d->exec[s]) != cudaSuccess) {
+            d->event_pool.push_back(shared);
+            shared = nullptr;
+            cudaGetLastError();
+        }
+    }
+    TaskState* owner = nullptr;
     for (pb2_gpu_task_t* t : ran) {
         TaskState* st = (TaskState*)t->reserved[0];
-        int rc = d->failed ? PB2_HOOK_RETURN_DISABLE : submit_finish(d, t, st);
+        int rc = d->failed ? PB2_HOOK_RETURN_DISABLE : submit_finish(d, t, st, shared);
         if (rc < 0) {
             abandon_submission(d, t, st, rc);
             failed.push_back({t, rc});
+        } else if (st->done_shared) {
+            owner = st;
         }
     }
+    if (owner) owner->done_shared = false;
+    else if (shared) d->event_pool.push_back(shared);
     batch.clear();
 }
 
@@ -1069,7 +1127,7 @@ static void submit_batch(pb2_device_s* d, std::vector<pb2_gpu_task_t*>& batch,
 static int try_stage(pb2_device_s* d, pb2_gpu_task_t* t) {
     int r = reserve_device_space(d, t);
     if (r != 0) return 1;
-    TaskState* st = new TaskState();
+    TaskState* st = new_state(d);
     t->reserved[0] = st;
     int rc = submit_stage_in(d, t, st);
     if (rc < 0) abandon_submission(d, t, st, rc);
@@ -1134,10 +1192,13 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
 // `rc = fetch_dec(mutex); if (1 == rc) leave` (:2742-2753).  Re-reading the counter instead would let two managers run.
 static bool progress_completions(pb2_device_s* d, bool* drained) {
     bool any = false;
+    cudaEvent_t done_seen = nullptr;
     for (auto& queue : d->inflight_q) {
         while (!queue.empty()) {
             InFlight f = queue.front();
-            cudaError_t q = cudaEventQuery(f.st->done);
+            // the tasks of a batch share one completion event: ask once
+            cudaError_t q = f.st->done == done_seen ? cudaSuccess : cudaEventQuery(f.st->done);
+            if (q == cudaSuccess) done_seen = f.st->done_shared ? f.st->done : nullptr;
             if (q == cudaErrorNotReady) break;
             if (q != cudaSuccess) {
                 fprintf(stderr, "[parsec_b200] device error while waiting for a task: %s\n", cudaGetErrorString(q));
@@ -1145,16 +1206,16 @@ static bool progress_completions(pb2_device_s* d, bool* drained) {
             }
             queue.pop_front();
             d->inflight_count--;
-            d->event_pool.push_back(f.st->done);
+            if (!f.st->done_shared) d->event_pool.push_back(f.st->done);
             any = true;
             if (f.st->is_w2r) {
                 complete_w2r(d, f.st);
-                delete f.st;
+                free_state(d, f.st);
                 continue;
             }
             pb2_gpu_task_t* t = f.task;
             finish_task(d, t, f.st);
-            delete f.st;
+            free_state(d, f.st);
             t->reserved[0] = nullptr;
             if (t->complete) t->complete(t, d->failed ? PB2_HOOK_RETURN_DISABLE : PB2_HOOK_RETURN_DONE, t->complete_cookie);
             if (d->params.trace_events)

@@ -201,6 +201,12 @@ __device__ __forceinline__ void dmma884p(double& d0, double& d1, double a, doubl
         : "d"(a), "d"(b));
 }
 
+// alpha * acc + beta * c with the roundings spelled out (one multiply, one fused multiply-add), so that every
+// instantiation of the tile code gives the same bits whatever the compiler would have contracted on its own
+__device__ __forceinline__ double axpby(double alpha, double acc, double beta, double c) {
+    return __fma_rn(beta, c, __dmul_rn(alpha, acc));
+}
+
 // One 128 x 128 tile of C = alpha A B + beta C; `tile` is its index among the tiles of this GEMM (column-major over
 // tiles).  Shared by the one-GEMM kernel and the grouped one.
 __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const CUtensorMap* mapB_p, int M, int N, int K,
@@ -361,8 +367,8 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     double2 v;
-                    v.x = alpha * acc[2 * q][j][e] + beta * old[c][q].x;
-                    v.y = alpha * acc[2 * q + 1][j][e] + beta * old[c][q].y;
+                    v.x = axpby(alpha, acc[2 * q][j][e], beta, old[c][q].x);
+                    v.y = axpby(alpha, acc[2 * q + 1][j][e], beta, old[c][q].y);
                     cp[q] = v;
                 }
             }
@@ -382,8 +388,8 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         double2 v;
-                        v.x = alpha * acc[2 * q][j][e];
-                        v.y = alpha * acc[2 * q + 1][j][e];
+                        v.x = __dmul_rn(alpha, acc[2 * q][j][e]);
+                        v.y = __dmul_rn(alpha, acc[2 * q + 1][j][e]);
                         cp[q] = v;
                     }
                 } else {
@@ -393,8 +399,8 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         double2 v;
-                        v.x = alpha * acc[2 * q][j][e] + beta * old[q].x;
-                        v.y = alpha * acc[2 * q + 1][j][e] + beta * old[q].y;
+                        v.x = axpby(alpha, acc[2 * q][j][e], beta, old[q].x);
+                        v.y = axpby(alpha, acc[2 * q + 1][j][e], beta, old[q].y);
                         cp[q] = v;
                     }
                 }
@@ -402,9 +408,7 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     if (row0 + i < M) {
-                        double r = alpha * acc[i][j][e];
-                        if (beta != 0.0) r += beta * cptr[i];
-                        cptr[i] = r;
+                        cptr[i] = beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, cptr[i]) : __dmul_rn(alpha, acc[i][j][e]);
                     }
                 }
             }

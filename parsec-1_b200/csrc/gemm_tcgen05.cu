@@ -584,12 +584,18 @@ gemm_umma_pair(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 //   * tiles are walked in a grouped raster (8 tile rows at a time), so that the A and B panels the pairs touch together
 //     fit in L2 for a large GEMM (the column-major walk of the per-tile kernel re-read them ~3x from DRAM at 8192^3).
 // Tensor maps travel in the kernel parameter space (one __grid_constant__ struct), like the per-tile kernels' do.
-constexpr int Q_STAGES = 5;          // operand ring: 5 x 32 KiB
-constexpr int Q_EBUF = 3;            // C boxes (32 x 32 fp32) per epilogue warp
+#ifndef PB2_Q_STAGES
+#define PB2_Q_STAGES 6
+#endif
+#ifndef PB2_Q_EBUF
+#define PB2_Q_EBUF 2
+#endif
+constexpr int Q_STAGES = PB2_Q_STAGES;  // operand ring: 6 x 32 KiB (5 stages + 3 C boxes measured 2 % slower)
+constexpr int Q_EBUF = PB2_Q_EBUF;      // C boxes (32 x 32 fp32) per epilogue warp
 constexpr int Q_RASTER = 8;          // tile rows per raster group
 constexpr int Q_TMEM_COLS = 512;     // two accumulator stages
 constexpr size_t grouped_smem() {
-    return (size_t)Q_STAGES * P_STAGE_BYTES + 4 * Q_EBUF * E_BOX_BYTES + 1024 + 1024;
+    return (size_t)Q_STAGES * P_STAGE_BYTES + 4 * Q_EBUF * E_BOX_BYTES + 1024 + 512;
 }
 
 struct UmmaTask {

@@ -9,7 +9,7 @@ import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-LIB_PATH = os.path.join(HERE, "libparsec_b200.so")
+LIB_PATH = os.environ.get("PB2_LIB") or os.path.join(HERE, "libparsec_b200.so")   # PB2_LIB: an A/B build (make variant)
 HEADER = os.path.join(ROOT, "include", "parsec_b200.h")
 
 SUCCESS = 0
