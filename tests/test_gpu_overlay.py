@@ -187,7 +187,16 @@ def test_two_gpus_in_one_process_share_tiles_over_nvlink(tmp_path):
     dump = str(tmp_path / "C.bin")
     out, err = run_app("overlay", ["-N", N, "-t", NB, "-c", 6, "--dump", dump], mca=("device_cuda_enabled", "2"))
     assert out["gpus"] == 2, err[-2000:]
-    norm = check_against_oracle(out, dump, N, NB)
+    # the reference's load balancer (parsec_get_best_device, device.c:121-171) may hand the first task of a chain to the
+    # CPU cores when both GPUs are loaded: every GEMM ran somewhere, and what ran on a GPU went through the module
+    d, A, B, Cref, cnt, ver = oracle_result(N, NB)
+    assert out["gemm_gpu"] + out["gemm_cpu"] == cnt.gemm and out["gemm_gpu"] > 0.9 * cnt.gemm
+    assert out["device_executed_tasks"] == out["gemm_gpu"]
+    assert out["c_version_min"] == out["c_version_max"] == N // NB and out["ab_version_max"] == 0
+    got = np.fromfile(dump, dtype=np.float64)
+    dense = lambda m: O.tiled_to_dense(d, m)
+    norm = O.parity_norm(dense(got), dense(Cref), dense(A), dense(B), N)
+    assert norm < 10.0, norm
     tile = NB * NB * 8
     tiles = 3 * (N // NB) ** 2
     assert out["d2d_bytes"] > 0                                   # some operand tiles came from the peer GPU
