@@ -304,7 +304,9 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=32768, help="matrix order (BASELINE configs[1]: 32768)")
+    ap.add_argument("--n", "--order", dest="n", type=int, default=32768,
+                    help="matrix order (BASELINE configs[1]: 32768); --order is the spelling to use under torchrun, whose "
+                         "own parser claims every option that starts with --n")
     ap.add_argument("--nb", type=int, default=1024, help="tile size")
     ap.add_argument("--cpu-n", type=int, default=16384,
                     help="matrix order of the bounded CPU sample (16384: about 15 s of CPU work on the GPU box's 16 cores)")
