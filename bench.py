@@ -359,8 +359,11 @@ def main():
     if args.replicas:   # diagnostic: every rank runs its own 1x1 problem, no data-plane traffic at all
         N, P, Q = args.n, 1, 1
     grid_rank = 0 if args.replicas else rank
-    comm = H.Comm(local_rank, P, Q, rank) if (world > 1 and not args.replicas) else None
     bf16 = args.dtype == "bf16"
+    # CTA budget of the NCCL communicators (comm_nccl.cu): an FP64 step needs ~10 GB/s of tile broadcasts per GPU and the
+    # DMMA kernel wants every SM, so 2 CTAs; a bf16 step computes 25x faster on the same tiles and needs ~80 GB/s
+    os.environ.setdefault("PB2_NCCL_MAX_CTAS", "8" if bf16 else "2")
+    comm = H.Comm(local_rank, P, Q, rank) if (world > 1 and not args.replicas) else None
     mtypes = (H.MATRIX_BF16, H.MATRIX_BF16, H.MATRIX_FLOAT) if bf16 else (H.MATRIX_DOUBLE,) * 3
     if bf16:
         try:   # driver-written cuBLAS bf16 peaks; a kernel timed inside a seconds-long step compares to the sustained one
