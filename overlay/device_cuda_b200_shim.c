@@ -720,6 +720,10 @@ int parsec_cuda_module_init( int dev_id, parsec_device_module_t **module )
         params.max_streams = parsec_cuda_max_streams;
     params.prefetch_deferred = 1;  /* a thread that only gives advice never becomes the device's manager */
     params.use_priorities = 1;     /* PARSEC_GPU_USE_PRIORITIES (device_gpu.h:20): task priorities order the pending list */
+    {   /* batched submissions for small tiles: not a reference parameter, so an environment name of this library */
+        const char *b = getenv("PB2_BATCH_BODIES");
+        if( NULL != b && atoi(b) > 1 ) params.batch_bodies = atoi(b);
+    }
 
     if( PB2_SUCCESS != pb2_device_create(dev_id, &params, &mod->pb2) ) {
         free(device->name); free(mod);
