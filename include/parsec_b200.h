@@ -217,6 +217,13 @@ typedef struct pb2_device_hooks_s {
     int (*data_alive)(pb2_device_t* dev, pb2_data_t* data, void* user);
 } pb2_device_hooks_t;
 int pb2_device_set_hooks(pb2_device_t* dev, const pb2_device_hooks_t* hooks);
+/* A device copy the USER allocated and attached by hand (cudaMalloc + parsec_data_copy_attach +
+ * parsec_data_transfer_ownership_to_copy, tests/dsl/ptg/cuda/nvlink_wrapper.c:189-206).  The module hands its address to
+ * task bodies and otherwise leaves it alone, as the reference does for copies without PARSEC_DATA_FLAG_PARSEC_OWNED
+ * (device_cuda_module.c:2161-2163, :2215, :2399): no staging, no eviction, no write-back, never freed by the module.
+ * A second call updates address / version / coherency.  PB2_ERR_EXISTS when the module already caches the tile itself. */
+int pb2_device_attach_user_copy(pb2_device_t* dev, pb2_data_t* data, void* device_ptr, uint32_t version, int coherency);
+int pb2_device_detach_user_copy(pb2_device_t* dev, pb2_data_t* data);
 /* Give back the HBM of `data`'s copy on this device (the runtime has destroyed the data; what the reference's LRU flush
  * does to detached copies, device_cuda_module.c:803-820).  The device must be idle or held by the caller (pb2_device_hold). */
 int pb2_device_drop_copy(pb2_device_t* dev, pb2_data_t* data);

@@ -25,7 +25,7 @@ prepare_tree() {   # $1 = destination
 configure_and_build() {   # $1 = source tree, $2 = build dir, $3 = extra C flags, $4 = extra shared-linker flags, $5 = extra libraries
     mkdir -p "$2"
     ( cd "$2" && cmake "$1" -G Ninja -DCMAKE_BUILD_TYPE=Release -DPARSEC_DIST_WITH_MPI=OFF -DSUPPORT_FORTRAN=OFF \
-        -DBUILD_TOOLS=OFF -DBUILD_TESTING=OFF -DPARSEC_PROF_TRACE=OFF -DPARSEC_GPU_WITH_CUDA=ON \
+        -DBUILD_TOOLS=OFF -DBUILD_TESTING=${TESTING:-OFF} -DPARSEC_PROF_TRACE=OFF -DPARSEC_GPU_WITH_CUDA=ON \
         -DCMAKE_CUDA_ARCHITECTURES=100 -DCMAKE_C_FLAGS="-include $REPO/overlay/nompi_shim.h $3" \
         -DCMAKE_SHARED_LINKER_FLAGS="$WORK/nompi_stub.o $4" -DCMAKE_C_STANDARD_LIBRARIES="-lm ${5:-}" > cmake.log 2>&1 \
       && ninja -j"$JOBS" parsec parsec-ptgpp > ninja.log 2>&1 ) || { tail -30 "$2/ninja.log" "$2/cmake.log" >&2; exit 4; }
@@ -47,9 +47,23 @@ cp "$REPO/overlay/device_cuda_b200_shim.c" "$WORK/src_overlay/parsec/mca/device/
 sed -i 's|list(APPEND MCA_${COMPONENT}_SOURCES mca/device/device_gpu.c mca/device/transfer_gpu.c)|# device_gpu.c and transfer_gpu.c are provided by device_cuda_b200_shim.c|' \
     "$WORK/src_overlay/parsec/mca/device/CMakeLists.txt"
 # libparsec.so finds libparsec_b200.so next to the repository it ships with: baseline/_ref/overlay -> parsec-1_b200
-configure_and_build "$WORK/src_overlay" "$WORK/build_overlay" "-I$REPO/include" \
+# the reference's own CUDA tests are built in this tree too (BUILD_TESTING); some of them name MPI without a guard:
+# overlay/teststub/mpi.h gives those names single-rank meanings
+TESTING=ON
+configure_and_build "$WORK/src_overlay" "$WORK/build_overlay" "-I$REPO/include -include $REPO/overlay/teststub/mpi.h -I$REPO/overlay/teststub" \
     "-Wl,-rpath,\\\$ORIGIN/../../../parsec-1_b200" "-L$REPO/parsec-1_b200 -lparsec_b200"
 cp -L "$WORK/build_overlay/parsec/libparsec.so.4" "$OUT/overlay/libparsec.so.4"
+# the reference's own CUDA tests, unmodified sources, linked against this tree (they run over either library)
+mkdir -p "$OUT/reftests"
+for t in nvlink stress stage testing_get_best_device; do
+    ( cd "$WORK/build_overlay" && ninja -j"$JOBS" $t > ninja_$t.log 2>&1 ) && cp "$WORK/build_overlay/tests/dsl/ptg/cuda/$t" "$OUT/reftests/$t" \
+        || echo "reference test $t did not build" >&2
+done
+for t in dtd_test_cuda_task_insert dtd_test_new_tile dtd_test_simple_gemm; do
+    ( cd "$WORK/build_overlay" && ninja -j"$JOBS" $t > ninja_$t.log 2>&1 ) && cp "$WORK/build_overlay/tests/dsl/dtd/$t" "$OUT/reftests/$t" \
+        || echo "reference test $t did not build" >&2
+done
+gcc -O1 -g -shared -fPIC "$REPO/overlay/teststub/segv_trace.c" -o "$OUT/reftests/libsegv_trace.so" -ldl -lpthread   # backtrace on a crash
 fi
 
 # the application: JDF -> C with the reference's own compiler, then gcc against the reference's headers

@@ -95,11 +95,21 @@ typedef struct b200_copy_s {
 PARSEC_OBJ_CLASS_DECLARATION(b200_copy_t);
 PARSEC_OBJ_CLASS_INSTANCE(b200_copy_t, parsec_data_copy_t, NULL, NULL);
 
+/* A device copy the user allocated and attached (nvlink_wrapper.c:189-206): a plain parsec_data_copy_t without
+ * PARSEC_DATA_FLAG_PARSEC_OWNED.  The module only hands its address to the bodies; the mirror exists so that the
+ * library knows the tile "is on the device". */
+typedef struct b200_foreign_s {
+    parsec_data_copy_t    *copy;
+    pb2_data_t            *data;
+    struct b200_foreign_s *next;
+} b200_foreign_t;
+
 typedef struct b200_module_s {
     parsec_device_cuda_module_t super;
     pb2_device_t               *pb2;
     int                         pb2_index;   /* device index inside libparsec_b200 (pb2_data_state_t.owner_device) */
     parsec_list_t               copies;      /* every b200_copy_t of this module (under b200_lock) */
+    struct b200_foreign_s      *foreign;     /* device copies the user attached by hand, and their mirrors */
     pb2_device_stats_t          folded;      /* what has been added to the parsec_device_module_t counters so far */
 } b200_module_t;
 
@@ -113,6 +123,7 @@ typedef struct b200_task_s {
     parsec_gpu_task_t *gpu_task;
     b200_module_t     *mod;
     b200_copy_t       *copy[MAX_PARAM_COUNT];
+    parsec_data_copy_t *foreign[MAX_PARAM_COUNT];   /* user-managed device copies among the flows */
 } b200_task_t;
 
 /* The execution stream of the thread that is inside parsec_cuda_kernel_scheduler.  Completions run on the thread
@@ -227,6 +238,27 @@ static b200_copy_t *b200_copy_of(b200_module_t *mod, parsec_data_t *original, pa
     return c->super.super.obj_class == &b200_copy_t_class ? (b200_copy_t*)c : NULL;
 }
 
+/* The mirror of a tile whose device copy belongs to the user; created on first sight, refreshed on every use. */
+static pb2_data_t *b200_foreign_mirror(b200_module_t *mod, parsec_data_t *original, parsec_data_copy_t *c,
+                                       parsec_data_copy_t *host)
+{
+    b200_foreign_t *f;
+    pthread_mutex_lock(&b200_lock);
+    for( f = mod->foreign; NULL != f && f->copy != c; f = f->next );
+    if( NULL == f ) {
+        f = (b200_foreign_t*)calloc(1, sizeof(b200_foreign_t));
+        f->copy = c;
+        f->data = pb2_data_create((uint64_t)original->key, NULL != original->dc ? (uint32_t)original->dc->dc_id : 0,
+                                  NULL != host ? host->device_private : NULL, original->nb_elts);
+        f->next = mod->foreign;
+        mod->foreign = f;
+    }
+    pthread_mutex_unlock(&b200_lock);
+    if( PB2_SUCCESS != pb2_device_attach_user_copy(mod->pb2, f->data, c->device_private, c->version, (int)c->coherency_state) )
+        return NULL;
+    return f->data;
+}
+
 /* Drop a copy (the data is gone, or the module shuts down), and the mirror with its last copy.  Only while this
  * device is idle (its manager seat is held by the caller); b200_lock held. */
 static void b200_retire_copy(b200_module_t *mod, b200_copy_t *bc)
@@ -302,6 +334,7 @@ static void b200_bind_flows(b200_task_t *bt, uint32_t mask)
     parsec_task_t *task = bt->gpu_task->ec;
     for( int i = 0; i < bt->pb2.nb_flows; i++ ) {
         b200_copy_t *bc = bt->copy[i];
+        if( NULL != bt->foreign[i] && (mask & (1u << i)) ) task->data[i].data_out = bt->foreign[i];
         if( NULL == bc || !(mask & (1u << i)) ) continue;
         b200_refresh_copy(bt->mod, bc, NULL);
         bc->super.device_private = bt->pb2.flow_dev_ptr[i];
@@ -440,8 +473,19 @@ parsec_cuda_kernel_scheduler( parsec_execution_stream_t *es, parsec_gpu_task_t *
          * data_out (read-only flows are not rewritten by the epilog) */
         parsec_data_copy_t *host = (0 == in->device_index) ? in : original->device_copies[0];
         if( NULL == host ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }
+        parsec_data_copy_t *mine = original->device_copies[mod->super.super.super.device_index];
+        if( NULL != mine && mine->super.super.obj_class != &b200_copy_t_class ) {
+            /* a device copy the user attached: its address goes to the body as it is (device_cuda_module.c:2161-2163) */
+            pb2_data_t *fm = b200_foreign_mirror(mod, original, mine, host);
+            if( NULL == fm ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }
+            bt->foreign[i] = mine;
+            t->flow_data[i] = fm;
+            t->flow_access[i] = access;
+            t->flow_nb_elts[i] = gpu_task->flow_nb_elts[i];
+            continue;
+        }
         b200_copy_t *bc = b200_copy_of(mod, original, host, gpu_task->flow_nb_elts[i]);
-        if( NULL == bc ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }  /* user-managed copy: leave it to another chore */
+        if( NULL == bc ) { free(bt); return PARSEC_HOOK_RETURN_NEXT; }
         pb2_data_sync_host(bc->mirror->data, host->device_private, host->version,
                            PARSEC_DATA_COHERENCY_OWNED == host->coherency_state ? PB2_DATA_COHERENCY_OWNED : -1);
         bt->copy[i] = bc;
@@ -809,6 +853,13 @@ int parsec_cuda_module_fini(parsec_device_module_t *device)
 
     b200_fold_stats(mod);
     b200_collect(mod, 1);
+    while( NULL != mod->foreign ) {
+        b200_foreign_t *f = mod->foreign;
+        mod->foreign = f->next;
+        pb2_device_detach_user_copy(mod->pb2, f->data);
+        pb2_data_destroy(f->data);
+        free(f);
+    }
     for( int j = 0; j < gpu_device->num_exec_streams; j++ ) {
         parsec_gpu_exec_stream_t *exec_stream = gpu_device->exec_stream[j];
         free(exec_stream->name);

@@ -959,6 +959,15 @@ static int submit_stage_in(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
     bool issued = false;
     for (int i = 0; i < t->nb_flows; ++i) {
         if (!(t->flow_access[i] & PB2_FLOW_ACCESS_RW) || !t->flow_data[i]) continue;
+        {   // a device copy the user allocated and attached (nvlink_wrapper.c:189-206): the module only hands its address
+            // to the body -- no staging, no readers, no version, no LRU (device_cuda_module.c:2161-2163, :2215, :2399)
+            pb2_copy_t* c = t->flow_data[i]->device_copies[d->device_index];
+            if (c && !(c->flags & PB2_FLAG_OWNED)) {
+                t->flow_dev_ptr[i] = c->device_private;
+                t->flow_host_ptr[i] = t->flow_data[i]->host_copy.device_private;
+                continue;
+            }
+        }
         int rc = stage_in_flow(d, t, st, i, &issued);
         if (rc < 0) return rc;
         pb2_copy_t* c = t->flow_data[i]->device_copies[d->device_index];
@@ -1020,7 +1029,10 @@ static int submit_finish(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st, cuda
     }
     uint32_t out_mask = 0;
     for (int i = 0; i < t->nb_flows; ++i)
-        if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && (t->pushout & (1 << i))) out_mask |= 1u << i;
+        if ((t->flow_access[i] & PB2_FLOW_ACCESS_WRITE) && (t->pushout & (1 << i)) && t->flow_data[i]) {
+            const pb2_copy_t* c = t->flow_data[i]->device_copies[d->device_index];
+            if (c && (c->flags & PB2_FLAG_OWNED)) out_mask |= 1u << i;  // a user's device copy is never staged out (:2215)
+        }
     if (shared && !out_mask) {
         st->done = shared;
         st->done_shared = true;
@@ -1142,6 +1154,7 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
         pb2_data_s* original = t->flow_data[i];
         std::lock_guard<std::mutex> g(original->lock);
         pb2_copy_t* gpu = original->device_copies[d->device_index];
+        if (!(gpu->flags & PB2_FLAG_OWNED)) continue;  // the user's own device copy: not ours to book
         bool d2h = false;
         if (type & PB2_FLOW_ACCESS_READ) {
             gpu->readers--;
@@ -1168,6 +1181,7 @@ static void finish_task(pb2_device_s* d, pb2_gpu_task_t* t, TaskState* st) {
         std::lock_guard<std::mutex> g(original->lock);
         pb2_copy_t* gpu = original->device_copies[d->device_index];
         pb2_copy_t* cpu = &original->host_copy;
+        if (!(gpu->flags & PB2_FLAG_OWNED)) continue;
         gpu->coherency_state = PB2_DATA_COHERENCY_SHARED;
         cpu->coherency_state = PB2_DATA_COHERENCY_SHARED;
         cpu->version = gpu->version;
@@ -1611,6 +1625,39 @@ extern "C" int pb2_device_drop_copy(pb2_device_t* d, pb2_data_t* data) {
     pb2_copy_t* c = data->device_copies[d->device_index];
     if (!c) return PB2_ERR_NOT_FOUND;
     release_copy(d, c);
+    return PB2_SUCCESS;
+}
+
+// A device copy allocated by the user (cudaMalloc) and attached to the data by hand, as tests/dsl/ptg/cuda/
+// nvlink_wrapper.c:189-206 does with parsec_data_copy_attach + parsec_data_transfer_ownership_to_copy: the module uses
+// the address as it is and keeps its hands off (no staging, no eviction, no write-back, never freed here).  Calling it
+// again updates the address.
+extern "C" int pb2_device_attach_user_copy(pb2_device_t* d, pb2_data_t* data, void* device_ptr, uint32_t version, int coherency) {
+    if (!d || !data || !device_ptr) return PB2_ERR_BAD_PARAM;
+    std::lock_guard<std::mutex> g(data->lock);
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (c && (c->flags & PB2_FLAG_OWNED)) return PB2_ERR_EXISTS;  // the module already caches this tile itself
+    if (!c) {
+        c = new pb2_copy_t();
+        c->flags = 0;
+        c->device_index = (int8_t)d->device_index;
+        c->original = data;
+        c->data_transfer_status = PB2_XFER_COMPLETE;
+        data->device_copies[d->device_index] = c;
+    }
+    c->device_private = device_ptr;
+    c->version = version;
+    c->coherency_state = (uint8_t)coherency;
+    if (coherency == PB2_DATA_COHERENCY_OWNED) data->owner_device = (int8_t)d->device_index;
+    return PB2_SUCCESS;
+}
+extern "C" int pb2_device_detach_user_copy(pb2_device_t* d, pb2_data_t* data) {
+    if (!d || !data) return PB2_ERR_BAD_PARAM;
+    std::lock_guard<std::mutex> g(data->lock);
+    pb2_copy_t* c = data->device_copies[d->device_index];
+    if (!c || (c->flags & PB2_FLAG_OWNED)) return PB2_ERR_NOT_FOUND;
+    data->device_copies[d->device_index] = nullptr;
+    delete c;
     return PB2_SUCCESS;
 }
 
