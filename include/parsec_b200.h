@@ -436,6 +436,54 @@ int pb2_gemm_taskpool_run(pb2_taskpool_t* tp, pb2_gemm_stats_t* stats);
 void pb2_gemm_taskpool_free(pb2_taskpool_t* tp);
 
 /* ------------------------------------------------------------------------------------------------
+ * Comm-engine transport for the ranks of one box (piece 3).
+ * What the reference does with MPI inside parsec/parsec_mpi_funnelled.c -- active messages on persistent receives
+ * (:621-703, :994-1008, :1103-1154), put/get as Isend/Irecv pairs plus a completion message (:793-991), the
+ * barrier (:1200) -- done over one shared-memory segment per job: a single-producer / single-consumer ring per
+ * ordered pair of ranks, and put as ONE copy by the origin into the target's address space (process_vm_writev;
+ * through the ring where the kernel refuses that).  Per-pair FIFO order.  Host memory.  The parsec_comm_engine_t
+ * vtable (parsec/parsec_comm_engine.h:161-182) over these is overlay/comm_engine_b200.c.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pb2_ce_s pb2_ce_t;
+typedef struct {
+    void* base;
+    size_t len;
+} pb2_ce_iov_t;
+typedef struct {
+    uint64_t sent_msgs, recv_msgs; /* active messages */
+    uint64_t put_bytes;            /* bytes moved by pb2_ce_put */
+    uint64_t staged_bytes;         /* of which through the ring (0 when single-copy put is available) */
+    int32_t single_copy;           /* 1: process_vm_writev in use */
+} pb2_ce_stats_t;
+typedef void (*pb2_ce_recv_fn)(void* user, int src, uint64_t tag, const void* msg, size_t len);
+
+/* Collective over the `world` ranks of job `job` (any string unique to the launch; the segment is /dev/shm/pb2ce.<job>).
+ * ring_bytes: capacity of each pair's ring, a power of two >= 4096, 0 = 1 MiB.  Returns when every rank has attached
+ * (PB2_ERR_NOT_FOUND after 120 s). */
+int pb2_ce_attach(const char* job, int rank, int world, size_t ring_bytes, pb2_ce_t** ce);
+int pb2_ce_detach(pb2_ce_t* ce); /* the last rank out removes the segment */
+int pb2_ce_rank(const pb2_ce_t* ce);
+int pb2_ce_world(const pb2_ce_t* ce);
+size_t pb2_ce_max_message(const pb2_ce_t* ce); /* largest len pb2_ce_send accepts (ring_bytes / 4 - 16) */
+void pb2_ce_mark_failed(pb2_ce_t* ce);         /* a rank that aborts: the others' waits return PB2_ERROR */
+/* send_am (parsec_comm_engine.h:122-125).  Any thread.  PB2_HOOK_RETURN_AGAIN (-1) when dst's ring is full: the
+ * caller keeps the message and retries after dst has polled. */
+int pb2_ce_send(pb2_ce_t* ce, int dst, uint64_t tag, const void* msg, size_t len);
+/* progress (:127): delivers at most max_msgs (0 = all) pending messages to fn, in per-source FIFO order; msg is valid
+ * during the call only.  One thread at a time; fn may call pb2_ce_send.  Returns the number delivered. */
+int pb2_ce_poll(pb2_ce_t* ce, pb2_ce_recv_fn fn, void* user, int max_msgs);
+/* While a put that goes through the ring waits for room it delivers this rank's incoming messages to fn (two ranks
+ * putting to each other would otherwise wait for each other).  Call pb2_ce_put outside pb2_ce_poll callbacks. */
+void pb2_ce_set_wait_poll(pb2_ce_t* ce, pb2_ce_recv_fn fn, void* user);
+/* put (:97-105): copies local[0..nlocal) of this process into remote[0..nremote) of rank dst (addresses valid in dst's
+ * address space; same total length).  Complete on return; a message sent to dst afterwards is seen after the data. */
+int pb2_ce_put(pb2_ce_t* ce, int dst, const pb2_ce_iov_t* local, int nlocal, const pb2_ce_iov_t* remote, int nremote);
+int pb2_ce_barrier(pb2_ce_t* ce);                                            /* sync (:146) */
+int pb2_ce_allreduce_i64(pb2_ce_t* ce, int64_t* vals, int n, int op);        /* n <= 16; op 0 max, 1 sum, 2 min */
+int pb2_ce_allgather(pb2_ce_t* ce, const void* mine, size_t bytes, void* all); /* bytes <= 128 per rank */
+int pb2_ce_stats(const pb2_ce_t* ce, pb2_ce_stats_t* out);
+
+/* ------------------------------------------------------------------------------------------------
  * DTD front-end: the second caller of the same device boundary (GPU tasks only).
  * parsec_dtd_taskpool_new + parsec_context_add_taskpool/start; parsec_dtd_insert_task_with_task_class
  * (parsec/interfaces/dtd/insert_function.c) with parsec_dtd_gpu_task_submit (:2359-2406);
