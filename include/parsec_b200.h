@@ -478,6 +478,9 @@ void pb2_ce_set_wait_poll(pb2_ce_t* ce, pb2_ce_recv_fn fn, void* user);
 /* put (:97-105): copies local[0..nlocal) of this process into remote[0..nremote) of rank dst (addresses valid in dst's
  * address space; same total length).  Complete on return; a message sent to dst afterwards is seen after the data. */
 int pb2_ce_put(pb2_ce_t* ce, int dst, const pb2_ce_iov_t* local, int nlocal, const pb2_ce_iov_t* remote, int nremote);
+/* get (:107-120): the mirror image, remote[] of rank src into local[]; PB2_ERR_NOT_SUPPORTED (-7) where the box has no
+ * cross-memory attach -- the caller then asks the peer to put (overlay/comm_engine_b200.c does). */
+int pb2_ce_get(pb2_ce_t* ce, int src, const pb2_ce_iov_t* local, int nlocal, const pb2_ce_iov_t* remote, int nremote);
 int pb2_ce_barrier(pb2_ce_t* ce);                                            /* sync (:146) */
 int pb2_ce_allreduce_i64(pb2_ce_t* ce, int64_t* vals, int n, int op);        /* n <= 16; op 0 max, 1 sum, 2 min */
 int pb2_ce_allgather(pb2_ce_t* ce, const void* mine, size_t bytes, void* all); /* bytes <= 128 per rank */

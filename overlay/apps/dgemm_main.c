@@ -13,8 +13,13 @@
  * the overlay libparsec (overlay/device_cuda_b200_shim.c + libparsec_b200.so); the library is chosen at run time
  * (LD_LIBRARY_PATH), nothing here knows which one it got.
  *
+ * Built against the distributed tree (overlay/build_dist.sh: PARSEC_HAVE_MPI, the comm engine of
+ * overlay/comm_engine_b200.c, ranks started by overlay/pb2run) the same file is one rank of a P x Q grid: it creates and
+ * fills the tiles it owns, and every rank prints its own line; --dump / --versions then name ONE file that the ranks
+ * fill together, each at the offsets of its own tiles.
+ *
  * usage: dgemm_NN_app [-N n | -M m -n n -K k] [-t nb] [-c cores] [-r runs] [--cublas] [--dump file] [--release] [--decline k]
- *                     [--versions file.json] [--cpu-tile lib.so:symbol] [-- parsec/MCA arguments]
+ *                     [--versions file.json] [--cpu-tile lib.so:symbol] [-P p] [-Q q] [-- parsec/MCA arguments]
  */
 #include "parsec.h"
 #include "parsec/data_dist/matrix/matrix.h"
@@ -26,11 +31,17 @@
 #include "parsec/execution_stream.h"
 
 #include <dlfcn.h>
+#include <fcntl.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/time.h>
+#include <unistd.h>
+
+#if defined(PARSEC_HAVE_MPI)
+#include <mpi.h>
+#endif
 
 #if defined(PARSEC_HAVE_CUDA)
 #include <cublas_v2.h>
@@ -72,10 +83,18 @@ static void fill_tile(double *tile, int m, int n, int mb, int nb, int M, unsigne
     }
 }
 
+static int grid_rank = 0, grid_P = 1, grid_Q = 1;
+
+static int is_mine(parsec_matrix_block_cyclic_t *dc, int tm, int tn)
+{
+    return (int)dc->super.super.rank_of(&dc->super.super, tm, tn) == grid_rank;
+}
+
 static parsec_matrix_block_cyclic_t *new_matrix(const char *name, int m, int n, int mb, int nb, unsigned seed)
 {
     parsec_matrix_block_cyclic_t *dc = (parsec_matrix_block_cyclic_t*)calloc(1, sizeof(*dc));
-    parsec_matrix_block_cyclic_init(dc, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_TILE, 0, mb, nb, m, n, 0, 0, m, n, 1, 1, 1, 1, 0, 0);
+    parsec_matrix_block_cyclic_init(dc, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_TILE, grid_rank, mb, nb, m, n, 0, 0, m, n,
+                                    grid_P, grid_Q, 1, 1, 0, 0);
     size_t bytes = (size_t)dc->super.nb_local_tiles * (size_t)dc->super.bsiz * sizeof(double);
     dc->mat = parsec_data_allocate(bytes);
     if( NULL == dc->mat ) { fprintf(stderr, "cannot allocate %zu bytes for %s\n", bytes, name); exit(2); }
@@ -83,6 +102,7 @@ static parsec_matrix_block_cyclic_t *new_matrix(const char *name, int m, int n, 
     #pragma omp parallel for collapse(2) schedule(dynamic, 1)
     for( int tn = 0; tn < dc->super.nt; tn++ )
         for( int tm = 0; tm < dc->super.mt; tm++ ) {
+            if( !is_mine(dc, tm, tn) ) continue;
             parsec_data_t *d = dc->super.super.data_of(&dc->super.super, tm, tn);
             fill_tile((double*)parsec_data_get_ptr(d, 0), tm, tn, mb, nb, m, seed);
         }
@@ -119,7 +139,7 @@ int main(int argc, char **argv)
     int M = 2048, N = 2048, K = 2048, NB = 256, cores = -1, runs = 1, use_cublas = 0, release = 0, decline_k = -1;
     const char *dump = NULL, *cpu_tile_spec = NULL, *versions_path = NULL;
     dgemm_cpu_tile_t cpu_tile = NULL;
-    int pargc = 1;
+    int pargc = 1, world = 1, want_P = 0, want_Q = 0;
     char **pargv = (char**)calloc((size_t)argc + 1, sizeof(char*));
     pargv[0] = argv[0];
     for( int i = 1; i < argc; i++ ) {
@@ -137,6 +157,8 @@ int main(int argc, char **argv)
         else if( !strcmp(argv[i], "--dump") && i + 1 < argc ) dump = argv[++i];
         else if( !strcmp(argv[i], "--cpu-tile") && i + 1 < argc ) cpu_tile_spec = argv[++i];
         else if( !strcmp(argv[i], "--versions") && i + 1 < argc ) versions_path = argv[++i];
+        else if( !strcmp(argv[i], "-P") && i + 1 < argc ) want_P = atoi(argv[++i]);
+        else if( !strcmp(argv[i], "-Q") && i + 1 < argc ) want_Q = atoi(argv[++i]);
         else { fprintf(stderr, "unknown argument %s\n", argv[i]); return 2; }
     }
     if( NULL != cpu_tile_spec ) {   /* lib.so:symbol -- a faster tile routine for the CPU incarnation */
@@ -148,6 +170,18 @@ int main(int argc, char **argv)
         if( NULL == cpu_tile ) { fprintf(stderr, "cannot resolve %s: %s\n", cpu_tile_spec, dlerror()); return 2; }
         free(spec);
     }
+
+#if defined(PARSEC_HAVE_MPI)
+    {
+        int provided;
+        if( MPI_SUCCESS != MPI_Init_thread(&argc, &argv, MPI_THREAD_SERIALIZED, &provided) ) return 1;
+        MPI_Comm_size(MPI_COMM_WORLD, &world);
+        MPI_Comm_rank(MPI_COMM_WORLD, &grid_rank);
+    }
+#endif
+    grid_P = want_P > 0 ? want_P : (want_Q > 0 ? world / want_Q : 1);
+    grid_Q = want_Q > 0 ? want_Q : world / grid_P;
+    if( grid_P * grid_Q != world ) { fprintf(stderr, "a %d x %d grid does not hold %d ranks\n", grid_P, grid_Q, world); return 2; }
 
     parsec_context_t *parsec = parsec_init(cores, &pargc, &pargv);
     if( NULL == parsec ) { fprintf(stderr, "parsec_init failed\n"); return 1; }
@@ -210,6 +244,7 @@ int main(int argc, char **argv)
     uint32_t vmin = ~0u, vmax = 0, vab = 0;
     for( int tn = 0; tn < dcC->super.nt; tn++ )
         for( int tm = 0; tm < dcC->super.mt; tm++ ) {
+            if( !is_mine(dcC, tm, tn) ) continue;
             parsec_data_t *d = dcC->super.super.data_of(&dcC->super.super, tm, tn);
             uint32_t v = parsec_data_get_copy(d, 0)->version;
             if( v < vmin ) vmin = v;
@@ -217,24 +252,30 @@ int main(int argc, char **argv)
         }
     for( int tn = 0; tn < dcA->super.nt; tn++ )
         for( int tm = 0; tm < dcA->super.mt; tm++ ) {
+            if( !is_mine(dcA, tm, tn) ) continue;
             uint32_t v = parsec_data_get_copy(dcA->super.super.data_of(&dcA->super.super, tm, tn), 0)->version;
             if( v > vab ) vab = v;
         }
     for( int tn = 0; tn < dcB->super.nt; tn++ )
         for( int tm = 0; tm < dcB->super.mt; tm++ ) {
+            if( !is_mine(dcB, tm, tn) ) continue;
             uint32_t v = parsec_data_get_copy(dcB->super.super.data_of(&dcB->super.super, tm, tn), 0)->version;
             if( v > vab ) vab = v;
         }
 
     if( NULL != versions_path ) {   /* version of the host copy of every tile: A, B, C, tiles column-major */
-        FILE *f = fopen(versions_path, "w");
-        if( NULL == f ) { perror(versions_path); return 1; }
+        char path[4096];   /* several ranks: one file per rank, -1 for the tiles of the others */
+        if( world > 1 ) snprintf(path, sizeof(path), "%s.%d", versions_path, grid_rank);
+        else snprintf(path, sizeof(path), "%s", versions_path);
+        FILE *f = fopen(path, "w");
+        if( NULL == f ) { perror(path); return 1; }
         parsec_matrix_block_cyclic_t *dcs[3] = { dcA, dcB, dcC };
         fprintf(f, "{");
         for( int which = 0; which < 3; which++ ) {
             fprintf(f, "%s\"%c\": [", which ? ", " : "", "ABC"[which]);
             for( int tn = 0; tn < dcs[which]->super.nt; tn++ )
                 for( int tm = 0; tm < dcs[which]->super.mt; tm++ ) {
+                    if( !is_mine(dcs[which], tm, tn) ) { fprintf(f, "%s-1", (tn || tm) ? ", " : ""); continue; }
                     parsec_data_t *d = dcs[which]->super.super.data_of(&dcs[which]->super.super, tm, tn);
                     fprintf(f, "%s%u", (tn || tm) ? ", " : "", parsec_data_get_copy(d, 0)->version);
                 }
@@ -244,23 +285,33 @@ int main(int argc, char **argv)
         fclose(f);
     }
 
-    if( NULL != dump ) {   /* C in tile storage, tiles in data_of order (column-major over tiles) */
-        FILE *f = fopen(dump, "wb");
-        if( NULL == f ) { perror(dump); return 1; }
+    if( NULL != dump ) {   /* C in tile storage, tiles in data_of order (column-major over tiles); every rank writes its own */
+        int fd = open(dump, O_CREAT | O_WRONLY, 0644);
+        if( fd < 0 ) { perror(dump); return 1; }
+        const size_t tile_bytes = sizeof(double) * (size_t)NB * NB;
         for( int tn = 0; tn < dcC->super.nt; tn++ )
             for( int tm = 0; tm < dcC->super.mt; tm++ ) {
+                if( !is_mine(dcC, tm, tn) ) continue;
                 parsec_data_t *d = dcC->super.super.data_of(&dcC->super.super, tm, tn);
-                fwrite(parsec_data_get_ptr(d, 0), sizeof(double), (size_t)NB * NB, f);
+                const char *src = (const char*)parsec_data_get_ptr(d, 0);
+                off_t at = (off_t)((size_t)tn * dcC->super.mt + tm) * (off_t)tile_bytes;
+                for( size_t done = 0; done < tile_bytes; ) {
+                    ssize_t w = pwrite(fd, src + done, tile_bytes - done, at + (off_t)done);
+                    if( w <= 0 ) { perror("pwrite"); return 1; }
+                    done += (size_t)w;
+                }
             }
-        fclose(f);
+        close(fd);
     }
 
     double flops = 2.0 * (double)M * (double)N * (double)K;
-    printf("{\"M\": %d, \"N\": %d, \"K\": %d, \"NB\": %d, \"runs\": %d, \"cores\": %d, \"gpus\": %d, \"cublas\": %d, "
+    printf("{\"rank\": %d, \"world\": %d, \"P\": %d, \"Q\": %d, "
+           "\"M\": %d, \"N\": %d, \"K\": %d, \"NB\": %d, \"runs\": %d, \"cores\": %d, \"gpus\": %d, \"cublas\": %d, "
            "\"seconds_best\": %.6f, \"seconds_first\": %.6f, \"gflops_best\": %.3f, \"gflops_first\": %.3f, "
            "\"read_a\": %lld, \"read_b\": %lld, \"gemm_cpu\": %lld, \"gemm_gpu\": %lld, \"device_executed_tasks\": %llu, "
            "\"c_version_min\": %u, \"c_version_max\": %u, \"ab_version_max\": %u, "
            "\"h2d_bytes\": %llu, \"d2d_bytes\": %llu, \"d2h_bytes\": %llu}\n",
+           grid_rank, world, grid_P, grid_Q,
            M, N, K, NB, runs, parsec->virtual_processes[0]->nb_cores, nb_gpus, use_cublas, best, first,
            flops / best * 1e-9, flops / first * 1e-9, (long long)dgemm_NN_count[0], (long long)dgemm_NN_count[1],
            (long long)dgemm_NN_count[2], (long long)dgemm_NN_count[3], (unsigned long long)executed_on_gpu,
@@ -281,5 +332,8 @@ int main(int argc, char **argv)
     parsec_tiled_matrix_destroy(&dcA->super); parsec_tiled_matrix_destroy(&dcB->super); parsec_tiled_matrix_destroy(&dcC->super);
     free(dcA); free(dcB); free(dcC);
     parsec_fini(&parsec);
+#if defined(PARSEC_HAVE_MPI)
+    MPI_Finalize();
+#endif
     return 0;
 }

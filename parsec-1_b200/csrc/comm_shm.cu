@@ -367,6 +367,52 @@ extern "C" int pb2_ce_put(pb2_ce_t* ce, int dst, const pb2_ce_iov_t* local, int 
     return PB2_SUCCESS;
 }
 
+// Origin-side read of remote[] of rank src into local[]: the mirror image of put, one copy, only where the kernel
+// allows cross-memory attach (PB2_ERR_NOT_SUPPORTED otherwise: the caller asks the peer to put instead).
+extern "C" int pb2_ce_get(pb2_ce_t* ce, int src, const pb2_ce_iov_t* local, int nlocal, const pb2_ce_iov_t* remote,
+                          int nremote) {
+    if (!ce || src < 0 || src >= ce->world || nlocal < 0 || nremote < 0 || (nlocal && !local) || (nremote && !remote))
+        return PB2_ERR_BAD_PARAM;
+    size_t lbytes = 0, rbytes = 0;
+    for (int i = 0; i < nlocal; ++i) lbytes += local[i].len;
+    for (int i = 0; i < nremote; ++i) rbytes += remote[i].len;
+    if (lbytes != rbytes) return PB2_ERR_BAD_PARAM;
+    if (lbytes == 0) return PB2_SUCCESS;
+    if (src != ce->rank && !ce->cma_ok) return PB2_ERR_NOT_SUPPORTED;
+    int li = 0, ri = 0;
+    size_t lo = 0, ro = 0;
+    while (li < nlocal && ri < nremote) {  // one contiguous piece per call: tiles are a few large pieces
+        size_t n = local[li].len - lo;
+        if (remote[ri].len - ro < n) n = remote[ri].len - ro;
+        char* lp = (char*)local[li].base + lo;
+        char* rp = (char*)remote[ri].base + ro;
+        if (n) {
+            if (src == ce->rank) {
+                memmove(lp, rp, n);
+            } else {
+                for (size_t done = 0; done < n;) {
+                    iovec l{lp + done, n - done}, r{rp + done, n - done};
+                    ssize_t got = process_vm_readv((pid_t)ce->hdr->pids[src], &l, 1, &r, 1, 0);
+                    if (got <= 0) {
+                        if (done == 0 && li == 0 && lo == 0 && (errno == EPERM || errno == ENOSYS)) {
+                            ce->cma_ok = 0;
+                            return PB2_ERR_NOT_SUPPORTED;
+                        }
+                        return PB2_ERROR;
+                    }
+                    done += (size_t)got;
+                }
+            }
+        }
+        lo += n;
+        ro += n;
+        if (lo == local[li].len) ++li, lo = 0;
+        if (ro == remote[ri].len) ++ri, ro = 0;
+    }
+    ce->put_bytes += lbytes;
+    return PB2_SUCCESS;
+}
+
 extern "C" int pb2_ce_barrier(pb2_ce_t* ce) {
     if (!ce) return PB2_ERR_BAD_PARAM;
     SegHdr* h = ce->hdr;
