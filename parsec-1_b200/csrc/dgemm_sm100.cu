@@ -207,8 +207,19 @@ __device__ __forceinline__ double axpby(double alpha, double acc, double beta, d
     return __fma_rn(beta, c, __dmul_rn(alpha, acc));
 }
 
-// One 128 x 128 tile of C = alpha A B + beta C; `tile` is its index among the tiles of this GEMM (column-major over
-// tiles).  Shared by the one-GEMM kernel and the grouped one.
+// One 128 x 128 tile of C = alpha op(A) op(B) + beta C; `tile` is its index among the tiles of this GEMM (column-major
+// over tiles).  Shared by the one-GEMM kernels and the grouped one.
+//
+// Transposed operands (TA / TB = 1) change which of the two shared-memory layouts an operand arrives in, nothing
+// else: op(A) = A^T is stored with k contiguous, which is the layout B has in the N,N case (one box [128 rows][16 k]),
+// and op(B) = B^T is stored with n contiguous, the layout A has in the N,N case (8 boxes [16 k][16 cols]).  Each
+// operand therefore has two fragment loaders, both conflict free under the 128-byte hardware swizzle:
+//   "contiguous along its own dimension" (A: N, B: T): LDS.128 of two neighbouring rows (columns) at one k,
+//       quarter warp (g&1, t) -> chunk ((g&1)^(ks&1))*4 + (x^t), 8 distinct;
+//   "contiguous along k" (A: T, B: N): LDS.64, half warp (g&3, t) -> slot 4*(ks^(g&3)) + 2*((t>>1)^(x&1)) + (t&1).
+// What a loader implies is the order in which a thread's DMMA fragments map to rows (columns) of the warp tile; the
+// epilogue applies the same map.
+template <int TA, int TB>
 __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const CUtensorMap* mapB_p, int M, int N, int K,
                                                double alpha, double beta, double* __restrict__ C, int ldc, int tile) {
     const CUtensorMap& mapA = *mapA_p;
@@ -248,9 +259,19 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
                 if (kt >= T_STAGES) mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * T_STAGE_BYTES;
                 mbar_arrive_expect_tx(&full[stage], T_STAGE_BYTES);
+                if (TA == 0) {
 #pragma unroll
-                for (int b = 0; b < BM / 16; ++b) tma_load_2d(sa + b * 2048, &mapA, m0 + 16 * b, kt * BK, &full[stage]);
-                tma_load_2d(sa + T_A_BYTES, &mapB, kt * BK, n0, &full[stage]);
+                    for (int b = 0; b < BM / 16; ++b) tma_load_2d(sa + b * 2048, &mapA, m0 + 16 * b, kt * BK, &full[stage]);
+                } else {
+                    tma_load_2d(sa, &mapA, kt * BK, m0, &full[stage]);
+                }
+                if (TB == 0) {
+                    tma_load_2d(sa + T_A_BYTES, &mapB, kt * BK, n0, &full[stage]);
+                } else {
+#pragma unroll
+                    for (int b = 0; b < BN / 16; ++b)
+                        tma_load_2d(sa + T_A_BYTES + b * 2048, &mapB, n0 + 16 * b, kt * BK, &full[stage]);
+                }
                 if (++stage == T_STAGES) {
                     stage = 0;
                     phase ^= 1;
@@ -278,18 +299,30 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
     }
 
     // per-thread shared-memory offsets (bytes, relative to the stage base)
-    const uint32_t a_thread = (uint32_t)((4 * wm + (g >> 1)) * 2048 + t * 128);
+    // A, contiguous along m (TA = 0): box 4wm + (g>>1), half (g&1) of its 16 rows -> rows 8g .. 8g+7 of the warp tile
+    // A, contiguous along k (TA = 1): fragment i of this thread is row 16(i>>1) + 2g + (i&1)
+    const uint32_t a_thread = TA == 0 ? (uint32_t)((4 * wm + (g >> 1)) * 2048 + t * 128)
+                                      : (uint32_t)((64 * wm + 2 * g) * 128 + (t & 1) * 8);
     uint32_t a_off[2][4];
 #pragma unroll
     for (int p = 0; p < 2; ++p)
 #pragma unroll
         for (int q = 0; q < 4; ++q) a_off[p][q] = (uint32_t)(((((g & 1) ^ p) * 4) + (q ^ t)) * 16);
-    const uint32_t b_thread = (uint32_t)(T_A_BYTES + (32 * wn + 2 * g) * 128 + (t & 1) * 8);
+    // B, contiguous along k (TB = 0): fragment j is column 16(j>>1) + 2g + (j&1)
+    // B, contiguous along n (TB = 1): box 2wn + ((g>>1)&1), chunks 4(g&1) + 2(g>>2) + h -> columns
+    //                                 16((g>>1)&1) + 8(g&1) + 4(g>>2) + j
+    const uint32_t b_thread = TB == 0 ? (uint32_t)(T_A_BYTES + (32 * wn + 2 * g) * 128 + (t & 1) * 8)
+                                      : (uint32_t)(T_A_BYTES + (2 * wn + ((g >> 1) & 1)) * 2048 + t * 128);
     uint32_t b_x[4], b_par[2];
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) b_x[ks] = (uint32_t)((ks ^ (g & 3)) * 32);
     b_par[0] = (uint32_t)((t >> 1) * 16);
     b_par[1] = (uint32_t)(((t >> 1) ^ 1) * 16);
+    uint32_t bt_off[2][2];  // TB = 1: [ks&1][h]
+#pragma unroll
+    for (int p = 0; p < 2; ++p)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) bt_off[p][h] = (uint32_t)(((((g & 1) ^ p) * 4) + ((2 * (g >> 2) + h) ^ t)) * 16);
 
     double acc[8][4][2];
 #pragma unroll
@@ -299,12 +332,24 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 
     double a[2][8], b[2][4];
     auto load_frags = [&](int buf, uint32_t sb, int ks) {
-        const uint32_t ab = sb + a_thread + ks * 512;
+        if (TA == 0) {
+            const uint32_t ab = sb + a_thread + ks * 512;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) lds128(a[buf][2 * q], a[buf][2 * q + 1], ab + a_off[ks & 1][q]);
-        const uint32_t bb = sb + b_thread + b_x[ks];
+            for (int q = 0; q < 4; ++q) lds128(a[buf][2 * q], a[buf][2 * q + 1], ab + a_off[ks & 1][q]);
+        } else {
+            const uint32_t ab = sb + a_thread + b_x[ks];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) b[buf][j] = lds64(bb + (16 * (j >> 1) + (j & 1)) * 128 + b_par[j & 1]);
+            for (int i = 0; i < 8; ++i) a[buf][i] = lds64(ab + (16 * (i >> 1) + (i & 1)) * 128 + b_par[i & 1]);
+        }
+        if (TB == 0) {
+            const uint32_t bb = sb + b_thread + b_x[ks];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[buf][j] = lds64(bb + (16 * (j >> 1) + (j & 1)) * 128 + b_par[j & 1]);
+        } else {
+            const uint32_t bb = sb + b_thread + ks * 512;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) lds128(b[buf][2 * h], b[buf][2 * h + 1], bb + bt_off[ks & 1][h]);
+        }
     };
 
     if (KT > 0) {
@@ -340,9 +385,18 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
         }
     }
 
-    // Epilogue.  acc[i][j][e]: row = m0 + 64wm + 8g + i, col = n0 + 32wn + 16(j>>1) + 4t + 2e + (j&1).
-    const int row0 = m0 + wm * 64 + 8 * g;
-    const bool rows_full = (row0 + 8 <= M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1);
+    // Epilogue.  acc[i][j][e] is row row_of(i), column col_of(j, e) of C; the maps follow the fragment loaders above:
+    //   TA = 0: row = 8g + i                      TA = 1: row = 16(i>>1) + 2g + (i&1)
+    //   TB = 0: col = 16(j>>1) + 4t + 2e + (j&1)  TB = 1: col = 16(t&1) + 8e + 4(t>>1) + j
+    // Either way fragments 2q and 2q+1 are two neighbouring rows, so a thread moves double2's: pair q sits at
+    // row0 + 2q (TA = 0) or row0 + 16q (TA = 1).
+    const int row0 = m0 + wm * 64 + (TA == 0 ? 8 * g : 2 * g);
+    constexpr int QS = TA == 0 ? 1 : 8;  // distance between pairs, in double2's
+    auto col_of = [&](int j, int e) {
+        return n0 + wn * 32 + (TB == 0 ? 16 * (j >> 1) + 4 * t + 2 * e + (j & 1) : 16 * (t & 1) + 8 * e + 4 * (t >> 1) + j);
+    };
+    auto row_of = [&](int i) { return TA == 0 ? row0 + i : row0 + 16 * (i >> 1) + (i & 1); };
+    const bool rows_full = (row_of(7) < M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1);
     if (rows_full && beta != 0.0) {
         // C += A B (the task-graph case).  The old values of FOUR columns (16 x 16 bytes per thread) are requested
         // before the first one is used: two L2 round trips per thread instead of eight -- a load cannot move above the
@@ -353,15 +407,15 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int j = 2 * h + (c >> 1), e = c & 1;
-                const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+                const int col = col_of(j, e);
                 const double2* cp = reinterpret_cast<const double2*>(C + (size_t)row0 + (size_t)min(col, N - 1) * ldc);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) old[c][q] = cp[q];  // a column past N re-reads column N-1 and is dropped below
+                for (int q = 0; q < 4; ++q) old[c][q] = cp[q * QS];  // a column past N re-reads column N-1 and is dropped below
             }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int j = 2 * h + (c >> 1), e = c & 1;
-                const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+                const int col = col_of(j, e);
                 if (col >= N) continue;
                 double2* cp = reinterpret_cast<double2*>(C + (size_t)row0 + (size_t)col * ldc);
 #pragma unroll
@@ -369,7 +423,7 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
                     double2 v;
                     v.x = axpby(alpha, acc[2 * q][j][e], beta, old[c][q].x);
                     v.y = axpby(alpha, acc[2 * q + 1][j][e], beta, old[c][q].y);
-                    cp[q] = v;
+                    cp[q * QS] = v;
                 }
             }
         }
@@ -379,36 +433,37 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
     for (int j = 0; j < 4; ++j) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            const int col = n0 + wn * 32 + 16 * (j >> 1) + 4 * t + 2 * e + (j & 1);
+            const int col = col_of(j, e);
             if (col >= N) continue;
-            double* cptr = C + (size_t)row0 + (size_t)col * ldc;
             if (rows_full) {
-                double2* cp = reinterpret_cast<double2*>(cptr);
+                double2* cp = reinterpret_cast<double2*>(C + (size_t)row0 + (size_t)col * ldc);
                 if (beta == 0.0) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         double2 v;
                         v.x = __dmul_rn(alpha, acc[2 * q][j][e]);
                         v.y = __dmul_rn(alpha, acc[2 * q + 1][j][e]);
-                        cp[q] = v;
+                        cp[q * QS] = v;
                     }
                 } else {
                     double2 old[4];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) old[q] = cp[q];
+                    for (int q = 0; q < 4; ++q) old[q] = cp[q * QS];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         double2 v;
                         v.x = axpby(alpha, acc[2 * q][j][e], beta, old[q].x);
                         v.y = axpby(alpha, acc[2 * q + 1][j][e], beta, old[q].y);
-                        cp[q] = v;
+                        cp[q * QS] = v;
                     }
                 }
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    if (row0 + i < M) {
-                        cptr[i] = beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, cptr[i]) : __dmul_rn(alpha, acc[i][j][e]);
+                    const int row = row_of(i);
+                    if (row < M) {
+                        double* cptr = C + (size_t)row + (size_t)col * ldc;
+                        *cptr = beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, *cptr) : __dmul_rn(alpha, acc[i][j][e]);
                     }
                 }
             }
@@ -419,7 +474,15 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 __global__ void __launch_bounds__(T_THREADS, 1)
 dgemm_nn_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
              double alpha, double beta, double* __restrict__ C, int ldc) {
-    dgemm_tile_tma(&mapA, &mapB, M, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
+    dgemm_tile_tma<0, 0>(&mapA, &mapB, M, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
+}
+
+// The same tile code for transposed operands (N,T / T,N / T,T): what cublasDgemm_v2 accepts, at the same speed.
+template <int TA, int TB>
+__global__ void __launch_bounds__(T_THREADS, 1)
+dgemm_tma_trans(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
+                double alpha, double beta, double* __restrict__ C, int ldc) {
+    dgemm_tile_tma<TA, TB>(&mapA, &mapB, M, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
 }
 
 // Grouped launch: the tiles of several independent GEMMs (the tile tasks a task runtime has ready together) in ONE
@@ -446,7 +509,7 @@ __global__ void __launch_bounds__(T_THREADS, 1) dgemm_nn_tma_grouped(const __gri
 #pragma unroll 1
     while (t + 1 < g.ntasks && b >= g.t[t + 1].tile_begin) ++t;
     const DgemmTask& k = g.t[t];
-    dgemm_tile_tma(&k.mapA, &k.mapB, k.M, k.N, k.K, k.alpha, k.beta, k.C, k.ldc, b - k.tile_begin);
+    dgemm_tile_tma<0, 0>(&k.mapA, &k.mapB, k.M, k.N, k.K, k.alpha, k.beta, k.C, k.ldc, b - k.tile_begin);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -533,6 +596,9 @@ static int ensure_smem_attr() {
     e = cudaFuncSetAttribute(dgemm_nn_128x128, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DGEMM_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
     e = cudaFuncSetAttribute(dgemm_nn_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
     e = cudaFuncSetAttribute(dgemm_nn_tma_grouped<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
@@ -652,12 +718,17 @@ extern "C" int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, i
     cudaStream_t st = (cudaStream_t)stream;
     const bool aligned = (((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0 && !(lda & 1) && !(ldb & 1) &&
                          !(ldc & 1);
-    if (!ta && !tb && aligned && k > 0 && dgemm_impl() == 0) {
+    const bool batching = g_dbatch.open && g_dbatch.stream == stream;
+    if (aligned && k > 0 && dgemm_impl() == 0) {
         int rc = ensure_smem_attr();
         if (rc != PB2_SUCCESS) return rc;
+        // op(A) is m x k: stored m x k (m contiguous, boxes [16 m][16 k]) or, transposed, k x m (k contiguous, one box
+        // [16 k][128 m]); op(B) is k x n: stored k x n (k contiguous) or, transposed, n x k (n contiguous)
         CUtensorMap ma, mb;
-        if (get_tmap(&ma, A, m, k, lda, 0) || get_tmap(&mb, B, k, n, ldb, 1)) return PB2_ERR_CUDA;
-        if (g_dbatch.open && g_dbatch.stream == stream) {  // recorded; launched with the rest of the batch
+        if ((ta ? get_tmap(&ma, A, k, m, lda, 1) : get_tmap(&ma, A, m, k, lda, 0)) ||
+            (tb ? get_tmap(&mb, B, n, k, ldb, 0) : get_tmap(&mb, B, k, n, ldb, 1)))
+            return PB2_ERR_CUDA;
+        if (batching && !ta && !tb) {  // recorded; launched with the rest of the batch
             DgemmTask t;
             memset(&t, 0, sizeof(t));
             t.mapA = ma; t.mapB = mb; t.C = C; t.alpha = alpha; t.beta = beta; t.M = m; t.N = n; t.K = k; t.ldc = ldc;
@@ -669,9 +740,22 @@ extern "C" int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, i
             }
             return PB2_SUCCESS;
         }
+        if (batching) {  // not a recordable call: what was recorded so far goes first, stream order is call order
+            rc = dgemm_batch_launch(g_dbatch.tasks, st);
+            if (rc != PB2_SUCCESS) return g_dbatch.status = rc;
+        }
         dim3 grid(((m + BM - 1) / BM) * ((n + BN - 1) / BN));
-        dgemm_nn_tma<<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
-    } else if (!ta && !tb && aligned && k > 0 && m % BM == 0 && n % BN == 0 && k % BK == 0) {
+        if (!ta && !tb) dgemm_nn_tma<<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+        else if (!ta && tb) dgemm_tma_trans<0, 1><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+        else if (ta && !tb) dgemm_tma_trans<1, 0><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+        else dgemm_tma_trans<1, 1><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, m, n, k, alpha, beta, C, ldc);
+        return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+    }
+    if (batching) {
+        int rc = dgemm_batch_launch(g_dbatch.tasks, st);
+        if (rc != PB2_SUCCESS) return g_dbatch.status = rc;
+    }
+    if (!ta && !tb && aligned && k > 0 && m % BM == 0 && n % BN == 0 && k % BK == 0) {
         int rc = ensure_smem_attr();
         if (rc != PB2_SUCCESS) return rc;
         dim3 grid((m / BM) * (n / BN));

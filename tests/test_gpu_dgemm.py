@@ -74,6 +74,44 @@ def test_transposes(ta, tb):
     assert r < 10
 
 
+@pytest.mark.parametrize("ta,tb", [("T", "N"), ("N", "T"), ("T", "T")])
+@pytest.mark.parametrize("m,n,k", [(1024, 1024, 1024), (1000, 936, 520), (129, 127, 18), (130, 70, 34), (64, 200, 2048),
+                                   (2, 2, 2), (128, 128, 16)])
+def test_transposed_operands_on_the_tma_path(ta, tb, m, n, k):
+    """Even leading dimensions: N,T / T,N / T,T run the same TMA + DMMA tile code as N,N (the operand only arrives in
+    the other shared-memory layout).  Every element of C is accumulated over k in the same order whatever the
+    layouts, so the result must be BIT-identical to the N,N call on explicitly transposed copies."""
+    r, got, want = _run(ta, tb, m, n, k, -1.0, 1.0, seed=m + 3 * n + 7 * k)      # C -= op(A) op(B): the update of a Cholesky / LU step
+    assert r < 10
+    r_nn, got_nn, _ = _run("N", "N", m, n, k, -1.0, 1.0, seed=m + 3 * n + 7 * k)  # same seed: same op(A), op(B), C
+    assert r_nn < 10 and np.array_equal(got, got_nn)
+    assert _run(ta, tb, m, n, k, 0.75, 0.0, seed=1, lda_pad=4)[0] < 10
+
+
+def test_transposed_operands_run_at_the_speed_of_nn():
+    import torch
+    n = 4096
+    g = torch.Generator(device="cuda").manual_seed(2)
+    A = torch.rand(n, n, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    B = torch.rand(n, n, dtype=torch.float64, device="cuda", generator=g) - 0.5
+    Cm = torch.zeros(n, n, dtype=torch.float64, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    rate = {}
+    for ta, tb in (("N", "N"), ("N", "T"), ("T", "N"), ("T", "T")):
+        for _ in range(2):
+            assert H.dgemm(ta, tb, n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, Cm.data_ptr(), n, s) == 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            H.dgemm(ta, tb, n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, Cm.data_ptr(), n, s)
+        e1.record()
+        torch.cuda.synchronize()
+        rate[ta + tb] = 5 * 2.0 * n ** 3 / (e0.elapsed_time(e1) * 1e-3) * 1e-12
+    print("fp64 4096^3 TFLOP/s:", {k: round(v, 2) for k, v in rate.items()})
+    for k, v in rate.items():
+        assert v > 0.9 * rate["NN"], rate
+
+
 def test_padded_leading_dimensions_and_odd_ld():
     assert _run("N", "N", 256, 128, 64, 1.0, 1.0, seed=7, lda_pad=6)[0] < 10   # even ld: TMA path
     assert _run("N", "N", 256, 128, 64, 1.0, 1.0, seed=8, lda_pad=3)[0] < 10   # odd ld: generic path
