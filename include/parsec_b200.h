@@ -68,6 +68,34 @@ int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, int k, doubl
 int parsec_b200_dgemm(char transa, char transb, int m, int n, int k, double alpha, const double* A, int lda,
                       const double* B, int ldb, double beta, double* C, int ldc, void* stream);
 
+/* Replaces cublasDsyrk_v2(handle, uplo, trans, n, k, &alpha, A, lda, &beta, C, ldc), the rank-k update of a tiled
+ * Cholesky (the HERK / SYRK body DPLASMA supplies to this runtime): trans = 'N': C = alpha A A^T + beta C with A n x k,
+ * 'T': C = alpha A^T A + beta C with A k x n; only the `uplo` ('L' / 'U') triangle of C is read and written.  Same
+ * TMA + DMMA tile code as parsec_b200_dgemm, blocks on the other side of the diagonal skipped. */
+int parsec_b200_dsyrk_sm100(char uplo, char trans, int n, int k, double alpha, const double* A, int lda, double beta,
+                            double* C, int ldc, void* stream);
+int parsec_b200_dsyrk(char uplo, char trans, int n, int k, double alpha, const double* A, int lda, double beta, double* C,
+                      int ldc, void* stream);
+
+/* Replaces cublasDtrsm_v2(handle, side, uplo, trans, diag, m, n, &alpha, T, ldt, B, ldb): B <- alpha * B * op(T)^-1
+ * (side 'R') or alpha * op(T)^-1 * B (side 'L'), T triangular ('L' / 'U'), diag 'N' / 'U'.  The 128 x 128 diagonal
+ * blocks of T are inverted in one launch, everything else is parsec_b200_dgemm on the block columns (rows).  Needs
+ * scratch in device memory: parsec_b200_dtrsm_workspace(side, m, n) bytes, which a CUDA body takes from
+ * parsec_gpu_pop_workspace (parsec/mca/device/device_gpu.c:168-246; pb2_device_pop_workspace here). */
+size_t parsec_b200_dtrsm_workspace(char side, int m, int n);
+int parsec_b200_dtrsm_sm100(char side, char uplo, char trans, char diag, int m, int n, double alpha, const double* T,
+                            int ldt, double* B, int ldb, void* workspace, size_t workspace_bytes, void* stream);
+int parsec_b200_dtrsm(char side, char uplo, char trans, char diag, int m, int n, double alpha, const double* T, int ldt,
+                      double* B, int ldb, void* workspace, size_t workspace_bytes, void* stream);
+/* The two halves on their own, for a DAG that solves many tiles against the same triangular tile (every TRSM of a
+ * Cholesky panel): invert the diagonal blocks once -- Tinv takes ceil(n / 128) blocks of 128 x 128 doubles -- and hand
+ * them to each solve; the workspace of the solve then only holds the m x n scratch (any size that
+ * parsec_b200_dtrsm_workspace returns is enough).  diag is a property of the inversion; the solve does not need it. */
+int parsec_b200_dtrtri_diag_sm100(char uplo, char diag, int n, const double* T, int ldt, double* Tinv, void* stream);
+int parsec_b200_dtrsm_inv_sm100(char side, char uplo, char trans, int m, int n, double alpha, const double* T, int ldt,
+                                const double* Tinv, double* B, int ldb, void* workspace, size_t workspace_bytes,
+                                void* stream);
+
 /* BF16-in / FP32-accumulate tile GEMM on tcgen05 + TMEM fed by TMA (BASELINE config 5).  Same argument meaning as
  * cublasGemmEx(CUDA_R_16BF, CUDA_R_16BF, CUDA_R_32F, CUBLAS_COMPUTE_32F): A, B are bf16, C is fp32, column-major.
  * The reference has no bf16 body; the call shape follows its cublasDgemm_v2 bodies.  transa = transb = 'N' only

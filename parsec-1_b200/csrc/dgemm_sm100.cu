@@ -219,7 +219,9 @@ __device__ __forceinline__ double axpby(double alpha, double acc, double beta, d
 //   "contiguous along k" (A: T, B: N): LDS.64, half warp (g&3, t) -> slot 4*(ks^(g&3)) + 2*((t>>1)^(x&1)) + (t&1).
 // What a loader implies is the order in which a thread's DMMA fragments map to rows (columns) of the warp tile; the
 // epilogue applies the same map.
-template <int TA, int TB>
+// TRI = 1 / 2: only the lower / upper triangle of C (diagonal included) is computed and written -- the rank-k update
+// C = alpha A A^T + beta C (SYRK) is this code with B = A; blocks entirely on the other side leave at once.
+template <int TA, int TB, int TRI = 0>
 __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const CUtensorMap* mapB_p, int M, int N, int K,
                                                double alpha, double beta, double* __restrict__ C, int ldc, int tile) {
     const CUtensorMap& mapA = *mapA_p;
@@ -236,6 +238,8 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
     const int bm = tile % tiles_m, bn = tile / tiles_m;
     const int m0 = bm * BM, n0 = bn * BN;
     const int KT = (K + BK - 1) / BK;
+    if (TRI == 1 && bn > bm) return;  // BM == BN: block (bm, bn) lies above / below the diagonal as a whole
+    if (TRI == 2 && bn < bm) return;
 
     if (tid == 0) {
         for (int s = 0; s < T_STAGES; ++s) {
@@ -396,7 +400,7 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
         return n0 + wn * 32 + (TB == 0 ? 16 * (j >> 1) + 4 * t + 2 * e + (j & 1) : 16 * (t & 1) + 8 * e + 4 * (t >> 1) + j);
     };
     auto row_of = [&](int i) { return TA == 0 ? row0 + i : row0 + 16 * (i >> 1) + (i & 1); };
-    const bool rows_full = (row_of(7) < M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1);
+    const bool rows_full = (row_of(7) < M) && ((((uintptr_t)C) & 15) == 0) && !(ldc & 1) && !(TRI != 0 && bm == bn);
     if (rows_full && beta != 0.0) {
         // C += A B (the task-graph case).  The old values of FOUR columns (16 x 16 bytes per thread) are requested
         // before the first one is used: two L2 round trips per thread instead of eight -- a load cannot move above the
@@ -461,6 +465,8 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int row = row_of(i);
+                    if (TRI == 1 && row < col) continue;  // diagonal block of a triangular update
+                    if (TRI == 2 && row > col) continue;
                     if (row < M) {
                         double* cptr = C + (size_t)row + (size_t)col * ldc;
                         *cptr = beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, *cptr) : __dmul_rn(alpha, acc[i][j][e]);
@@ -483,6 +489,14 @@ __global__ void __launch_bounds__(T_THREADS, 1)
 dgemm_tma_trans(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K,
                 double alpha, double beta, double* __restrict__ C, int ldc) {
     dgemm_tile_tma<TA, TB>(&mapA, &mapB, M, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
+}
+
+// C = alpha A A^T + beta C (TRANS = 0, A is n x k) or alpha A^T A + beta C (TRANS = 1, A is k x n) on one triangle of C.
+template <int TRANS, int TRI>
+__global__ void __launch_bounds__(T_THREADS, 1)
+dsyrk_tma(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int N, int K, double alpha,
+          double beta, double* __restrict__ C, int ldc) {
+    dgemm_tile_tma<TRANS, 1 - TRANS, TRI>(&mapA, &mapB, N, N, K, alpha, beta, C, ldc, (int)blockIdx.x);
 }
 
 // Grouped launch: the tiles of several independent GEMMs (the tile tasks a task runtime has ready together) in ONE
@@ -599,6 +613,10 @@ static int ensure_smem_attr() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(dgemm_tma_trans<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dsyrk_tma<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dsyrk_tma<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dsyrk_tma<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dsyrk_tma<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
     e = cudaFuncSetAttribute(dgemm_nn_tma_grouped<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM);
     if (e != cudaSuccess) return PB2_ERR_CUDA;
@@ -765,6 +783,59 @@ extern "C" int parsec_b200_dgemm_sm100(char transa, char transb, int m, int n, i
         dgemm_generic_64x64<<<grid, 128, 0, st>>>(ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc);
     }
     return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+// Symmetric rank-k update on one triangle of C, for the SYRK / HERK bodies of a tiled Cholesky:
+//   trans = 'N': C = alpha A A^T + beta C, A is n x k;  trans = 'T': C = alpha A^T A + beta C, A is k x n.
+// The other triangle of C is neither read nor written.
+__global__ void dsyrk_generic(int lower, int trans, int N, int K, double alpha, const double* __restrict__ A, int lda,
+                              double beta, double* __restrict__ C, int ldc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= N || j >= N || (lower ? i < j : i > j)) return;
+    double acc = 0.0;
+    for (int l = 0; l < K; ++l)
+        acc += trans ? A[(size_t)l + (size_t)i * lda] * A[(size_t)l + (size_t)j * lda]
+                     : A[(size_t)i + (size_t)l * lda] * A[(size_t)j + (size_t)l * lda];
+    double* c = C + (size_t)i + (size_t)j * ldc;
+    *c = beta != 0.0 ? pb2::axpby(alpha, acc, beta, *c) : __dmul_rn(alpha, acc);
+}
+
+extern "C" int parsec_b200_dsyrk_sm100(char uplo, char trans, int n, int k, double alpha, const double* A, int lda,
+                                        double beta, double* C, int ldc, void* stream) {
+    using namespace pb2;
+    const int tr = trans_of(trans);
+    const int lower = (uplo == 'L' || uplo == 'l') ? 1 : (uplo == 'U' || uplo == 'u') ? 0 : -1;
+    if (tr < 0 || lower < 0 || n < 0 || k < 0) return PB2_ERR_BAD_PARAM;
+    if (lda < (tr ? (k > 1 ? k : 1) : (n > 1 ? n : 1)) || ldc < (n > 1 ? n : 1)) return PB2_ERR_BAD_PARAM;
+    if (n == 0) return PB2_SUCCESS;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (g_dbatch.open && g_dbatch.stream == stream) {  // stream order is call order
+        int rc = dgemm_batch_launch(g_dbatch.tasks, st);
+        if (rc != PB2_SUCCESS) return g_dbatch.status = rc;
+    }
+    const bool aligned = (((uintptr_t)A | (uintptr_t)C) & 15) == 0 && !(lda & 1) && !(ldc & 1);
+    if (aligned && k > 0) {
+        int rc = ensure_smem_attr();
+        if (rc != PB2_SUCCESS) return rc;
+        CUtensorMap ma, mb;  // the two roles of A: op(A) and op(A)^T
+        if (tr ? (get_tmap(&ma, A, k, n, lda, 1) || get_tmap(&mb, A, k, n, lda, 1))
+               : (get_tmap(&ma, A, n, k, lda, 0) || get_tmap(&mb, A, n, k, lda, 0)))
+            return PB2_ERR_CUDA;
+        const int tiles = (n + BM - 1) / BM;
+        dim3 grid(tiles * tiles);
+        if (!tr && lower) dsyrk_tma<0, 1><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, n, k, alpha, beta, C, ldc);
+        else if (!tr) dsyrk_tma<0, 2><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, n, k, alpha, beta, C, ldc);
+        else if (lower) dsyrk_tma<1, 1><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, n, k, alpha, beta, C, ldc);
+        else dsyrk_tma<1, 2><<<grid, T_THREADS, T_SMEM, st>>>(ma, mb, n, k, alpha, beta, C, ldc);
+    } else {
+        dim3 block(16, 16), grid((n + 15) / 16, (n + 15) / 16);
+        dsyrk_generic<<<grid, block, 0, st>>>(lower, tr, n, k, alpha, A, lda, beta, C, ldc);
+    }
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+extern "C" int parsec_b200_dsyrk(char uplo, char trans, int n, int k, double alpha, const double* A, int lda, double beta,
+                                  double* C, int ldc, void* stream) {
+    return parsec_b200_dsyrk_sm100(uplo, trans, n, k, alpha, A, lda, beta, C, ldc, stream);
 }
 
 // dyld= lookup tries "<fn>_sm100" first and then "<fn>" (device_cuda_module.c:175-240).

@@ -1,0 +1,249 @@
+// dtrsm_sm100.cu -- parsec_b200_dtrsm: the triangular solve of a tile against a triangular tile, for the TRSM bodies of
+// a tiled Cholesky / LU (what DPLASMA hands this runtime as cublasDtrsm_v2 calls).
+//
+// B200-first shape of the algorithm: almost all of the work is GEMM, so almost all of it goes to the DMMA tile kernel.
+//   1. the 128 x 128 diagonal blocks of the triangular tile are inverted (one CTA each, a few microseconds, done
+//      concurrently for all of them);
+//   2. block column (row) j of the solution is ONE GEMM with the inverted block, and the blocks not yet solved are
+//      updated with ONE GEMM of depth 128 -- parsec_b200_dgemm_sm100 with the transposes the call asks for.
+// So a solve against an NB = 1024 tile is 8 inversions in one launch and 16 GEMM launches; substitution, the part
+// that does not parallelise, is confined to the 128 x 128 blocks.  The scratch (inverted blocks + one block column)
+// is the caller's: a CUDA body takes it from parsec_gpu_pop_workspace (device_gpu.c:168-246, here
+// pb2_device_pop_workspace), parsec_b200_dtrsm_workspace says how much.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "parsec_b200.h"
+#include "pb2_internal.h"
+
+namespace pb2 {
+
+constexpr int TB_NB = 128;                      // block size of the solve
+constexpr int TB_LD = TB_NB + 1;                // padded shared-memory row
+constexpr int TRTRI_THREADS = 256;
+constexpr size_t TRTRI_SMEM = ((size_t)TB_NB * TB_LD + 8 * 16 * 17) * sizeof(double);
+
+// Inverse of each diagonal block of the triangular matrix T (n x n, `lower` says which triangle is stored), written as
+// full 128 x 128 blocks (ld 128) with zeros in the other triangle.  One CTA per block, all in shared memory:
+//   1. the eight 16 x 16 diagonal sub-blocks by substitution (one thread per column: 16 short dependent steps);
+//   2. three doubling steps 16 -> 32 -> 64 -> 128 with  inv [A 0; C B] = [A^-1 0; -B^-1 C A^-1  B^-1]:  two small
+//      matrix products per step by all the threads, the product C A^-1 parked in the (empty) mirror block above the
+//      diagonal.  No step depends on more than 16 serial operations, against 128 for plain substitution.
+// An upper triangle is inverted as the transpose of a lower one.
+__global__ void __launch_bounds__(TRTRI_THREADS) trtri_diag_blocks(int n, int lower, int unit, const double* __restrict__ T,
+                                                                   int ldt, double* __restrict__ Tinv) {
+    extern __shared__ double sm[];
+    double* S = sm;                          // S[i * TB_LD + j]: the block, made lower triangular
+    double* X0 = sm + TB_NB * TB_LD;         // X0[(b * 16 + i) * 17 + c]: inverses of the 16 x 16 sub-blocks
+    const int blk = blockIdx.x, j0 = blk * TB_NB;
+    const int nb = n - j0 < TB_NB ? n - j0 : TB_NB;
+    const int tid = threadIdx.x;
+    const double* t = T + (size_t)j0 + (size_t)j0 * ldt;
+    for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
+        const int r = e % TB_NB, c = e / TB_NB;  // element (r, c) of the stored block, column-major: coalesced reads
+        double v = 0.0;
+        if (r < nb && c < nb) {
+            if (r == c) v = unit ? 1.0 : t[(size_t)r + (size_t)c * ldt];
+            else if (lower ? r > c : r < c) v = t[(size_t)r + (size_t)c * ldt];
+        } else if (r == c) {
+            v = 1.0;                             // identity padding of a ragged last block
+        }
+        if (lower) S[r * TB_LD + c] = v; else S[c * TB_LD + r] = v;
+    }
+    __syncthreads();
+    if (tid < TB_NB) {  // 1. sub-block b, column c
+        const int b = tid >> 4, c = tid & 15;
+        const double* L = S + (b * 16) * TB_LD + b * 16;
+        double* x = X0 + (b * 16) * 17 + c;
+        for (int i = 0; i < c; ++i) x[i * 17] = 0.0;
+        x[c * 17] = 1.0 / L[c * TB_LD + c];
+        for (int i = c + 1; i < 16; ++i) {
+            double acc = 0.0;
+            for (int k = c; k < i; ++k) acc = fma(L[i * TB_LD + k], x[k * 17], acc);
+            x[i * 17] = -acc / L[i * TB_LD + i];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < 8 * 256; e += TRTRI_THREADS) {
+        const int b = e >> 8, i = (e >> 4) & 15, c = e & 15;
+        S[(b * 16 + i) * TB_LD + b * 16 + c] = X0[(b * 16 + i) * 17 + c];
+    }
+    __syncthreads();
+    for (int sz = 16; sz < TB_NB; sz *= 2) {  // 2. pairs of inverted sz x sz blocks -> inverted 2sz x 2sz blocks
+        const int outputs = (TB_NB / (2 * sz)) * sz * sz;
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {   // tmp = C A^-1, parked in the mirror block
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            const double* Crow = S + (base + sz + i) * TB_LD + base;
+            const double* Ainv = S + base * TB_LD + base;
+            double acc = 0.0;
+            for (int k = j; k < sz; ++k) acc = fma(Crow[k], Ainv[k * TB_LD + j], acc);
+            S[(base + i) * TB_LD + base + sz + j] = acc;
+        }
+        __syncthreads();
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {   // C = -B^-1 tmp
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
+            const double* tmp = S + base * TB_LD + base + sz;
+            double acc = 0.0;
+            for (int k = 0; k <= i; ++k) acc = fma(Brow[k], tmp[k * TB_LD + j], acc);
+            S[(base + sz + i) * TB_LD + base + j] = -acc;
+        }
+        __syncthreads();
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            S[(base + i) * TB_LD + base + sz + j] = 0.0;
+        }
+        __syncthreads();
+    }
+    double* out = Tinv + (size_t)blk * TB_NB * TB_NB;
+    for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
+        const int r = e % TB_NB, c = e / TB_NB;
+        out[e] = lower ? S[r * TB_LD + c] : S[c * TB_LD + r];
+    }
+}
+
+__global__ void scale_matrix(int m, int n, double alpha, double* __restrict__ B, int ldb) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i < m && j < n) {
+        double* p = B + (size_t)i + (size_t)j * ldb;
+        *p = alpha == 0.0 ? 0.0 : alpha * *p;
+    }
+}
+
+static inline int flag(char c, char a, char b) {  // 1 for a, 0 for b, -1 otherwise (case-insensitive)
+    if (c == a || c == a + 32) return 1;
+    if (c == b || c == b + 32) return 0;
+    return -1;
+}
+
+}  // namespace pb2
+
+extern "C" size_t parsec_b200_dtrsm_workspace(char side, int m, int n) {
+    using namespace pb2;
+    const int right = flag(side, 'R', 'L');
+    if (right < 0 || m < 0 || n < 0) return 0;
+    const int tri = right ? n : m;
+    const size_t nblk = (size_t)(tri + TB_NB - 1) / TB_NB;
+    return (nblk * TB_NB * TB_NB + (size_t)((m + 1) & ~1) * (size_t)n) * sizeof(double) + 512;
+}
+
+namespace pb2 {
+static int ensure_trtri_attr() {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(trtri_diag_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRTRI_SMEM) != cudaSuccess)
+            return PB2_ERR_CUDA;
+        attr_set[dev] = true;
+    }
+    return PB2_SUCCESS;
+}
+
+// The solve proper, given the inverted diagonal blocks.  X is built in W (same shape as B, ld ldw) so that no step
+// reads and writes the same memory, and copied over B at the end: per block column (row) j
+//     W_j   =  B_j op(Tinv_jj)            (left:  op(Tinv_jj) B_j)
+//     B_rest -= W_j U(j, rest)             (left:  U(rest, j) W_j),     U = op(T)
+// two GEMM launches per block, nothing else in the chain.
+static int solve_with_inverses(int right, int lower, int tr, int m, int n, double alpha, const double* T, int ldt,
+                               const double* Tinv, double* B, int ldb, double* W, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (alpha != 1.0) scale_matrix<<<dim3((m + 127) / 128, n), 128, 0, st>>>(m, n, alpha, B, ldb);
+    const int tri = right ? n : m;
+    const int nblk = (tri + TB_NB - 1) / TB_NB;
+    // U = op(T) is upper triangular when T is upper and not transposed, or lower and transposed
+    const bool u_upper = (lower == 0) != (tr == 1);
+    const char tc = tr ? 'T' : 'N';
+    const bool forward = right ? u_upper : !u_upper;
+    const int ldw = (m + 1) & ~1;
+    for (int s = 0; s < nblk; ++s) {
+        const int j = forward ? s : nblk - 1 - s;
+        const int j0 = j * TB_NB, nbj = tri - j0 < TB_NB ? tri - j0 : TB_NB;
+        const int r0 = forward ? j0 + nbj : 0;  // the blocks not solved yet: [r0, r0 + nrest)
+        const int nrest = forward ? tri - r0 : j0;
+        const double* inv = Tinv + (size_t)j * TB_NB * TB_NB;
+        int rc;
+        if (right) {
+            double* Wj = W + (size_t)j0 * ldw;
+            rc = parsec_b200_dgemm_sm100('N', tc, m, nbj, nbj, 1.0, B + (size_t)j0 * ldb, ldb, inv, TB_NB, 0.0, Wj, ldw, stream);
+            if (rc != PB2_SUCCESS) return rc;
+            if (nrest > 0) {  // U(j, rest) = T(j, rest) or T(rest, j)^T
+                const double* Tp = tr ? T + (size_t)r0 + (size_t)j0 * ldt : T + (size_t)j0 + (size_t)r0 * ldt;
+                rc = parsec_b200_dgemm_sm100('N', tc, m, nrest, nbj, -1.0, Wj, ldw, Tp, ldt, 1.0, B + (size_t)r0 * ldb, ldb, stream);
+                if (rc != PB2_SUCCESS) return rc;
+            }
+        } else {
+            double* Wj = W + j0;
+            rc = parsec_b200_dgemm_sm100(tc, 'N', nbj, n, nbj, 1.0, inv, TB_NB, B + j0, ldb, 0.0, Wj, ldw, stream);
+            if (rc != PB2_SUCCESS) return rc;
+            if (nrest > 0) {  // U(rest, j) = T(rest, j) or T(j, rest)^T
+                const double* Tp = tr ? T + (size_t)j0 + (size_t)r0 * ldt : T + (size_t)r0 + (size_t)j0 * ldt;
+                rc = parsec_b200_dgemm_sm100(tc, 'N', nrest, n, nbj, -1.0, Tp, ldt, Wj, ldw, 1.0, B + r0, ldb, stream);
+                if (rc != PB2_SUCCESS) return rc;
+            }
+        }
+    }
+    if (cudaMemcpy2DAsync(B, (size_t)ldb * 8, W, (size_t)ldw * 8, (size_t)m * 8, n, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+        return PB2_ERR_CUDA;
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+static int parse(char side, char uplo, char trans, char diag, int* right, int* lower, int* tr, int* unit) {
+    *right = flag(side, 'R', 'L');
+    *lower = flag(uplo, 'L', 'U');
+    *unit = flag(diag, 'U', 'N');
+    *tr = (trans == 'N' || trans == 'n') ? 0 : (trans == 'T' || trans == 't' || trans == 'C' || trans == 'c') ? 1 : -1;
+    return (*right < 0 || *lower < 0 || *unit < 0 || *tr < 0) ? PB2_ERR_BAD_PARAM : PB2_SUCCESS;
+}
+static inline double* align256(void* p) { return reinterpret_cast<double*>(((uintptr_t)p + 255) & ~(uintptr_t)255); }
+}  // namespace pb2
+
+// Inverses of the 128 x 128 diagonal blocks of the triangular n x n matrix T, into Tinv: ceil(n / 128) blocks of
+// 128 x 128 doubles.  On its own so that a DAG can invert the diagonal tile of a panel ONCE and hand the result to
+// every solve of the panel (parsec_b200_dtrsm_inv).
+extern "C" int parsec_b200_dtrtri_diag_sm100(char uplo, char diag, int n, const double* T, int ldt, double* Tinv, void* stream) {
+    using namespace pb2;
+    const int lower = flag(uplo, 'L', 'U'), unit = flag(diag, 'U', 'N');
+    if (lower < 0 || unit < 0 || n < 0 || ldt < (n > 1 ? n : 1) || (n && (!T || !Tinv))) return PB2_ERR_BAD_PARAM;
+    if (n == 0) return PB2_SUCCESS;
+    int rc = ensure_trtri_attr();
+    if (rc != PB2_SUCCESS) return rc;
+    trtri_diag_blocks<<<(n + TB_NB - 1) / TB_NB, TRTRI_THREADS, TRTRI_SMEM, (cudaStream_t)stream>>>(n, lower, unit, T, ldt, Tinv);
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+extern "C" int parsec_b200_dtrsm_inv_sm100(char side, char uplo, char trans, int m, int n, double alpha, const double* T,
+                                            int ldt, const double* Tinv, double* B, int ldb, void* workspace,
+                                            size_t workspace_bytes, void* stream) {
+    using namespace pb2;
+    int right, lower, tr, unit;
+    if (parse(side, uplo, trans, 'N', &right, &lower, &tr, &unit) != PB2_SUCCESS || m < 0 || n < 0) return PB2_ERR_BAD_PARAM;
+    const int tri = right ? n : m;
+    if (ldt < (tri > 1 ? tri : 1) || ldb < (m > 1 ? m : 1)) return PB2_ERR_BAD_PARAM;
+    if (m == 0 || n == 0) return PB2_SUCCESS;
+    if (!workspace || !Tinv || workspace_bytes < (size_t)((m + 1) & ~1) * (size_t)n * sizeof(double) + 256) return PB2_ERR_BAD_PARAM;
+    return solve_with_inverses(right, lower, tr, m, n, alpha, T, ldt, Tinv, B, ldb, align256(workspace), stream);
+}
+
+extern "C" int parsec_b200_dtrsm_sm100(char side, char uplo, char trans, char diag, int m, int n, double alpha,
+                                        const double* T, int ldt, double* B, int ldb, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+    using namespace pb2;
+    int right, lower, tr, unit;
+    if (parse(side, uplo, trans, diag, &right, &lower, &tr, &unit) != PB2_SUCCESS || m < 0 || n < 0) return PB2_ERR_BAD_PARAM;
+    const int tri = right ? n : m;
+    if (ldt < (tri > 1 ? tri : 1) || ldb < (m > 1 ? m : 1)) return PB2_ERR_BAD_PARAM;
+    if (m == 0 || n == 0) return PB2_SUCCESS;
+    if (!workspace || workspace_bytes < parsec_b200_dtrsm_workspace(side, m, n)) return PB2_ERR_BAD_PARAM;
+    const int nblk = (tri + TB_NB - 1) / TB_NB;
+    double* Tinv = align256(workspace);
+    double* W = Tinv + (size_t)nblk * TB_NB * TB_NB;
+    int rc = parsec_b200_dtrtri_diag_sm100(uplo, diag, tri, T, ldt, Tinv, stream);
+    if (rc != PB2_SUCCESS) return rc;
+    return solve_with_inverses(right, lower, tr, m, n, alpha, T, ldt, Tinv, B, ldb, W, stream);
+}
+
+extern "C" int parsec_b200_dtrsm(char side, char uplo, char trans, char diag, int m, int n, double alpha, const double* T,
+                                  int ldt, double* B, int ldb, void* workspace, size_t workspace_bytes, void* stream) {
+    return parsec_b200_dtrsm_sm100(side, uplo, trans, diag, m, n, alpha, T, ldt, B, ldb, workspace, workspace_bytes, stream);
+}

@@ -83,6 +83,13 @@ def lib():
     vp, i32, i64, u32, u64, dbl, sz = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_uint64, C.c_double, C.c_size_t
     sig = {
         "parsec_b200_dgemm_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, dbl, vp, i32, vp, i32, dbl, vp, i32, vp]),
+        "parsec_b200_dsyrk_sm100": (i32, [C.c_char, C.c_char, i32, i32, dbl, vp, i32, dbl, vp, i32, vp]),
+        "parsec_b200_dtrsm_workspace": (C.c_size_t, [C.c_char, i32, i32]),
+        "parsec_b200_dtrtri_diag_sm100": (i32, [C.c_char, C.c_char, i32, vp, i32, vp, vp]),
+        "parsec_b200_dtrsm_inv_sm100": (i32, [C.c_char, C.c_char, C.c_char, i32, i32, dbl, vp, i32, vp, vp, i32, vp,
+                                              C.c_size_t, vp]),
+        "parsec_b200_dtrsm_sm100": (i32, [C.c_char, C.c_char, C.c_char, C.c_char, i32, i32, dbl, vp, i32, vp, i32, vp,
+                                          C.c_size_t, vp]),
         "parsec_b200_dgemm": (i32, [C.c_char, C.c_char, i32, i32, i32, dbl, vp, i32, vp, i32, dbl, vp, i32, vp]),
         "parsec_b200_gemm_bf16_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, C.c_float, vp, i32, vp, i32,
                                                C.c_float, vp, i32, vp]),
@@ -312,6 +319,19 @@ def tiled_gemm(A, B, Cm, dev, comm=None, **knobs):
         return {"nb_gemm": st.nb_gemm, "nb_read_a": st.nb_read_a, "nb_read_b": st.nb_read_b, "seconds": st.seconds}
     finally:
         lib().pb2_gemm_taskpool_free(tp)
+
+
+def dsyrk(uplo, trans, n, k, alpha, A_ptr, lda, beta, C_ptr, ldc, stream=0):
+    return lib().parsec_b200_dsyrk_sm100(uplo.encode(), trans.encode(), n, k, alpha, A_ptr, lda, beta, C_ptr, ldc, stream)
+
+
+def dtrsm_workspace(side, m, n):
+    return lib().parsec_b200_dtrsm_workspace(side.encode(), m, n)
+
+
+def dtrsm(side, uplo, trans, diag, m, n, alpha, T_ptr, ldt, B_ptr, ldb, ws_ptr, ws_bytes, stream=0):
+    return lib().parsec_b200_dtrsm_sm100(side.encode(), uplo.encode(), trans.encode(), diag.encode(), m, n, alpha, T_ptr, ldt,
+                                         B_ptr, ldb, ws_ptr, ws_bytes, stream)
 
 
 def dgemm(transa, transb, m, n, k, alpha, A_ptr, lda, B_ptr, ldb, beta, C_ptr, ldc, stream=0):
