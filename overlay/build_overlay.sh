@@ -4,7 +4,8 @@
 #   stock/    libparsec.so of the UNMODIFIED reference with its own CUDA module          (comparator + CPU arm)
 #   overlay/  libparsec.so with overlay/device_cuda_b200_shim.c in place of
 #             parsec/mca/device/cuda/device_cuda_module.c, device_gpu.c, transfer_gpu.c   (the drop-in)
-#   bin/      parsec-ptgpp, and dgemm_NN_app = overlay/apps/dgemm_NN.jdf through parsec-ptgpp + dgemm_main.c
+#   bin/      parsec-ptgpp, dgemm_NN_app = overlay/apps/dgemm_NN.jdf through parsec-ptgpp + dgemm_main.c, and
+#             dpotrf_L_app = overlay/apps/dpotrf_L.jdf + dpotrf_main.c (tiled Cholesky, TRSM / SYRK / GEMM bodies)
 # The work tree is a scratch copy under $WORK (default /tmp/parsec_b200_overlay); only binaries are installed.
 # Recipe for a build without MPI: SURVEY.md Appendix D.
 set -euo pipefail
@@ -76,6 +77,15 @@ gcc -O3 -fopenmp -ffp-contract=off $INC -c "$A/dgemm_NN.c" -o "$A/dgemm_NN.o"
 gcc -O3 -fopenmp -ffp-contract=off $INC -I"$A" -c "$A/dgemm_main.c" -o "$A/dgemm_main.o"
 gcc -fopenmp "$A/dgemm_main.o" "$A/dgemm_NN.o" -o "$OUT/bin/dgemm_NN_app" -L"$OUT/overlay" -l:libparsec.so.4 \
     -L/usr/local/cuda/lib64 -lcublas -lcudart -lm -lpthread -ldl -Wl,-rpath-link,"$REPO/parsec-1_b200"
+# the second application: tiled Cholesky over the same module, CUDA bodies calling the kernel library directly
+cp "$REPO/overlay/apps/dpotrf_L.jdf" "$REPO/overlay/apps/dpotrf_main.c" "$A/"
+( cd "$A" && "$B/parsec/interfaces/ptg/ptg-compiler/parsec-ptgpp" -E -i dpotrf_L.jdf -o dpotrf_L -f dpotrf_L > ptgpp_potrf.log 2>&1 ) \
+    || { cat "$A/ptgpp_potrf.log" >&2; exit 5; }
+gcc -O3 -fopenmp $INC -I"$REPO/include" -c "$A/dpotrf_L.c" -o "$A/dpotrf_L.o"
+gcc -O3 -fopenmp $INC -I"$REPO/include" -I"$A" -c "$A/dpotrf_main.c" -o "$A/dpotrf_main.o"
+gcc -fopenmp "$A/dpotrf_main.o" "$A/dpotrf_L.o" -o "$OUT/bin/dpotrf_L_app" -L"$OUT/overlay" -l:libparsec.so.4 \
+    -L"$REPO/parsec-1_b200" -lparsec_b200 -L/usr/local/cuda/lib64 -lcudart -lm -lpthread -ldl \
+    -Wl,-rpath,'$ORIGIN/../../../parsec-1_b200'
 [ -f "$OUT/bin/parsec-ptgpp" ] || cp "$B/parsec/interfaces/ptg/ptg-compiler/parsec-ptgpp" "$OUT/bin/parsec-ptgpp"
 nm -D --defined-only "$OUT/overlay/libparsec.so.4" | grep -E ' (parsec_cuda_kernel_scheduler|parsec_default_cuda_stage_(in|out)|parsec_cuda_module_(init|fini)|device_cuda_static_component|parsec_gpu_(pop|push|free)_workspace)$' > "$OUT/overlay/exported_symbols.txt"
 echo "installed:"; ls -la "$OUT/stock" "$OUT/overlay" "$OUT/bin"
