@@ -96,6 +96,17 @@ int parsec_b200_dtrsm_inv_sm100(char side, char uplo, char trans, int m, int n, 
                                 const double* Tinv, double* B, int ldb, void* workspace, size_t workspace_bytes,
                                 void* stream);
 
+/* Replaces cusolverDnDpotrf(handle, uplo, n, A, lda, work, lwork, devInfo): Cholesky factorisation of one tile in
+ * place, A = L L^T ('L') or U^T U ('U'); the other triangle is not touched.  Right-looking over 128-column blocks: the
+ * diagonal block is factored and its factor inverted by one CTA, the panel is a parsec_b200_dgemm with that inverse,
+ * the trailing update a parsec_b200_dsyrk.  workspace: parsec_b200_dpotrf_workspace(n) bytes of device memory;
+ * dev_info: device int, zeroed by the caller, receives the 1-based index of the first non-positive pivot (may be NULL). */
+size_t parsec_b200_dpotrf_workspace(int n);
+int parsec_b200_dpotrf_sm100(char uplo, int n, double* A, int lda, void* workspace, size_t workspace_bytes, int* dev_info,
+                             void* stream);
+int parsec_b200_dpotrf(char uplo, int n, double* A, int lda, void* workspace, size_t workspace_bytes, int* dev_info,
+                       void* stream);
+
 /* BF16-in / FP32-accumulate tile GEMM on tcgen05 + TMEM fed by TMA (BASELINE config 5).  Same argument meaning as
  * cublasGemmEx(CUDA_R_16BF, CUDA_R_16BF, CUDA_R_32F, CUBLAS_COMPUTE_32F): A, B are bf16, C is fp32, column-major.
  * The reference has no bf16 body; the call shape follows its cublasDgemm_v2 bodies.  transa = transb = 'N' only

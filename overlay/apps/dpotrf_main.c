@@ -7,7 +7,7 @@
  * dtd_test_simple_gemm.c:43-91 (seed 3872), N added to the diagonal (strictly diagonally dominant, so positive
  * definite); the upper triangle is never referenced.
  *
- * usage: dpotrf_L_app [-N n] [-t nb] [-c cores] [--dump file] [--cpu-trsm] [-- parsec/MCA arguments]
+ * usage: dpotrf_L_app [-N n] [-t nb] [-c cores] [--dump file] [--cpu-trsm] [--cpu-potrf] [-- parsec/MCA arguments]
  */
 #include "parsec.h"
 #include "parsec/data_dist/matrix/matrix.h"
@@ -25,7 +25,7 @@
 
 #include "dpotrf_L.h"
 
-int64_t dpotrf_L_count[8];
+int64_t dpotrf_L_count[9];
 
 /* ---- inputs: the generator of dtd_test_simple_gemm.c:43-91 (64-bit LCG with a jump-ahead per tile column; the value
  * is formed in single precision by a multiply and a subtract, each rounded) ---- */
@@ -65,7 +65,7 @@ static double now(void)
 
 int main(int argc, char **argv)
 {
-    int N = 2048, NB = 256, cores = -1, gpu_trsm = 1;
+    int N = 2048, NB = 256, cores = -1, gpu_trsm = 1, gpu_potrf = 1;
     const char *dump = NULL;
     int pargc = 1;
     char **pargv = (char**)calloc((size_t)argc + 1, sizeof(char*));
@@ -77,6 +77,7 @@ int main(int argc, char **argv)
         else if( !strcmp(argv[i], "-c") && i + 1 < argc ) cores = atoi(argv[++i]);
         else if( !strcmp(argv[i], "--dump") && i + 1 < argc ) dump = argv[++i];
         else if( !strcmp(argv[i], "--cpu-trsm") ) gpu_trsm = 0;
+        else if( !strcmp(argv[i], "--cpu-potrf") ) gpu_potrf = 0;
         else { fprintf(stderr, "unknown argument %s\n", argv[i]); return 2; }
     }
     parsec_context_t *parsec = parsec_init(cores, &pargc, &pargv);
@@ -105,7 +106,7 @@ int main(int argc, char **argv)
         if( NULL != dev && PARSEC_DEV_CUDA == dev->type ) dcA->super.super.register_memory(&dcA->super.super, dev);
     }
 
-    parsec_dpotrf_L_taskpool_t *tp = parsec_dpotrf_L_new(&dcA->super, gpu_trsm);
+    parsec_dpotrf_L_taskpool_t *tp = parsec_dpotrf_L_new(&dcA->super, gpu_trsm, gpu_potrf);
     parsec_add2arena(&tp->arenas_datatypes[PARSEC_dpotrf_L_DEFAULT_ADT_IDX], parsec_datatype_double_t,
                      PARSEC_MATRIX_FULL, 1, NB, NB, NB, PARSEC_ARENA_ALIGNMENT_SSE, -1);
     double t0 = now();
@@ -134,11 +135,11 @@ int main(int argc, char **argv)
         fclose(f);
     }
     printf("{\"N\": %d, \"NB\": %d, \"cores\": %d, \"gpus\": %d, \"seconds\": %.6f, \"gflops\": %.3f, "
-           "\"potrf\": %lld, \"trsm_cpu\": %lld, \"trsm_gpu\": %lld, \"syrk_cpu\": %lld, \"syrk_gpu\": %lld, "
+           "\"potrf\": %lld, \"potrf_gpu\": %lld, \"trsm_cpu\": %lld, \"trsm_gpu\": %lld, \"syrk_cpu\": %lld, \"syrk_gpu\": %lld, "
            "\"gemm_cpu\": %lld, \"gemm_gpu\": %lld, \"potrf_failures\": %lld, \"device_executed_tasks\": %llu, "
            "\"h2d_bytes\": %llu, \"d2d_bytes\": %llu, \"d2h_bytes\": %llu}\n",
            N, NB, parsec->virtual_processes[0]->nb_cores, nb_gpus, t, (double)N * N * N / 3.0 / t * 1e-9,
-           (long long)dpotrf_L_count[0], (long long)dpotrf_L_count[1], (long long)dpotrf_L_count[2], (long long)dpotrf_L_count[3],
+           (long long)(dpotrf_L_count[0] + dpotrf_L_count[8]), (long long)dpotrf_L_count[8], (long long)dpotrf_L_count[1], (long long)dpotrf_L_count[2], (long long)dpotrf_L_count[3],
            (long long)dpotrf_L_count[4], (long long)dpotrf_L_count[5], (long long)dpotrf_L_count[6], (long long)dpotrf_L_count[7],
            (unsigned long long)executed_on_gpu, (unsigned long long)h2d_bytes, (unsigned long long)d2d_bytes,
            (unsigned long long)d2h_bytes);

@@ -247,3 +247,171 @@ extern "C" int parsec_b200_dtrsm(char side, char uplo, char trans, char diag, in
                                   int ldt, double* B, int ldb, void* workspace, size_t workspace_bytes, void* stream) {
     return parsec_b200_dtrsm_sm100(side, uplo, trans, diag, m, n, alpha, T, ldt, B, ldb, workspace, workspace_bytes, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// parsec_b200_dpotrf: Cholesky factorisation of one tile on the GPU, for the POTRF body of the same DAG (what DPLASMA
+// hands the runtime as a cusolverDnDpotrf call).  Right-looking over 128-column blocks, and again almost all GEMM:
+//   potf2_trtri   the 128 x 128 diagonal block factored AND its factor inverted, one CTA, in shared memory
+//   panel         L21 = A21 L11^-T = A21 * inv(L11)^T : parsec_b200_dgemm with the inverse just computed
+//   trailing      A22 -= L21 L21^T                     : parsec_b200_dsyrk
+namespace pb2 {
+
+// Factor the nb x nb diagonal block (lower: A = L L^T; upper: A = U^T U, handled as the transpose) in place, and write
+// inv(L) (resp. inv(U)) as a full 128 x 128 block to `inv`.  Thread i owns row i: column j of L is a dot product of
+// length j per row, then one square root, then a scale.  *info = first non-positive pivot (1-based, offset by j0).
+__global__ void __launch_bounds__(TRTRI_THREADS) potf2_trtri(int nb, int lower, double* __restrict__ A, int lda,
+                                                             double* __restrict__ inv, int j0, int* __restrict__ info) {
+    extern __shared__ double sm[];
+    double* S = sm;
+    double* X0 = sm + TB_NB * TB_LD;
+    __shared__ int bad;
+    const int tid = threadIdx.x;
+    if (tid == 0) bad = 0;
+    for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
+        const int r = e % TB_NB, c = e / TB_NB;
+        double v = (r == c) ? 1.0 : 0.0;  // identity padding of a ragged block
+        if (r < nb && c < nb) v = (lower ? r >= c : r <= c) ? A[(size_t)r + (size_t)c * lda] : 0.0;
+        if (lower) S[r * TB_LD + c] = v; else S[c * TB_LD + r] = v;
+    }
+    __syncthreads();
+    for (int j = 0; j < nb; ++j) {
+        const int i = tid;
+        double s = 0.0;
+        if (i >= j && i < nb) {
+            double s0 = 0.0, s1 = 0.0;
+            int k = 0;
+            for (; k + 1 < j; k += 2) {
+                s0 = fma(S[i * TB_LD + k], S[j * TB_LD + k], s0);
+                s1 = fma(S[i * TB_LD + k + 1], S[j * TB_LD + k + 1], s1);
+            }
+            if (k < j) s0 = fma(S[i * TB_LD + k], S[j * TB_LD + k], s0);
+            s = S[i * TB_LD + j] - (s0 + s1);
+            if (i == j) {
+                if (!(s > 0.0)) {
+                    if (!bad) bad = j + 1;
+                    s = 1.0;  // keep going with something finite; the caller reads info
+                }
+                S[j * TB_LD + j] = sqrt(s);
+            }
+        }
+        __syncthreads();
+        if (i > j && i < nb) S[i * TB_LD + j] = s / S[j * TB_LD + j];
+        __syncthreads();
+    }
+    if (tid == 0 && bad && info && *info == 0) *info = j0 + bad;
+    for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {  // the factor goes back, the other triangle is left alone
+        const int r = e % TB_NB, c = e / TB_NB;
+        if (r < nb && c < nb && (lower ? r >= c : r <= c)) A[(size_t)r + (size_t)c * lda] = lower ? S[r * TB_LD + c] : S[c * TB_LD + r];
+    }
+    __syncthreads();
+    // the inverse of the factor: same steps as trtri_diag_blocks
+    if (tid < TB_NB) {
+        const int b = tid >> 4, c = tid & 15;
+        const double* L = S + (b * 16) * TB_LD + b * 16;
+        double* x = X0 + (b * 16) * 17 + c;
+        for (int i = 0; i < c; ++i) x[i * 17] = 0.0;
+        x[c * 17] = 1.0 / L[c * TB_LD + c];
+        for (int i = c + 1; i < 16; ++i) {
+            double acc = 0.0;
+            for (int k = c; k < i; ++k) acc = fma(L[i * TB_LD + k], x[k * 17], acc);
+            x[i * 17] = -acc / L[i * TB_LD + i];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < 8 * 256; e += TRTRI_THREADS) {
+        const int b = e >> 8, i = (e >> 4) & 15, c = e & 15;
+        S[(b * 16 + i) * TB_LD + b * 16 + c] = X0[(b * 16 + i) * 17 + c];
+    }
+    __syncthreads();
+    for (int sz = 16; sz < TB_NB; sz *= 2) {
+        const int outputs = (TB_NB / (2 * sz)) * sz * sz;
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            const double* Crow = S + (base + sz + i) * TB_LD + base;
+            const double* Ainv = S + base * TB_LD + base;
+            double acc = 0.0;
+            for (int k = j; k < sz; ++k) acc = fma(Crow[k], Ainv[k * TB_LD + j], acc);
+            S[(base + i) * TB_LD + base + sz + j] = acc;
+        }
+        __syncthreads();
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
+            const double* tmp = S + base * TB_LD + base + sz;
+            double acc = 0.0;
+            for (int k = 0; k <= i; ++k) acc = fma(Brow[k], tmp[k * TB_LD + j], acc);
+            S[(base + sz + i) * TB_LD + base + j] = -acc;
+        }
+        __syncthreads();
+        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
+            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
+            S[(base + i) * TB_LD + base + sz + j] = 0.0;
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
+        const int r = e % TB_NB, c = e / TB_NB;
+        inv[e] = lower ? S[r * TB_LD + c] : S[c * TB_LD + r];
+    }
+}
+
+}  // namespace pb2
+
+extern "C" size_t parsec_b200_dpotrf_workspace(int n) {
+    if (n < 0) return 0;
+    return ((size_t)pb2::TB_NB * pb2::TB_NB + (size_t)((n + 1) & ~1) * pb2::TB_NB) * sizeof(double) + 512;
+}
+
+// A = L L^T ('L') or U^T U ('U') in place; the other triangle is not touched.  *dev_info (device memory, may be NULL;
+// set it to 0 before the call) receives the index of the first non-positive pivot, as cusolverDnDpotrf's devInfo does.
+extern "C" int parsec_b200_dpotrf_sm100(char uplo, int n, double* A, int lda, void* workspace, size_t workspace_bytes,
+                                         int* dev_info, void* stream) {
+    using namespace pb2;
+    const int lower = flag(uplo, 'L', 'U');
+    if (lower < 0 || n < 0 || lda < (n > 1 ? n : 1)) return PB2_ERR_BAD_PARAM;
+    if (n == 0) return PB2_SUCCESS;
+    if (!A || !workspace || workspace_bytes < parsec_b200_dpotrf_workspace(n)) return PB2_ERR_BAD_PARAM;
+    cudaStream_t st = (cudaStream_t)stream;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(potf2_trtri, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRTRI_SMEM) != cudaSuccess)
+            return PB2_ERR_CUDA;
+        attr_set[dev] = true;
+    }
+    double* inv = align256(workspace);
+    double* W = inv + (size_t)TB_NB * TB_NB;
+    const int ldw = (n + 1) & ~1;
+    for (int j0 = 0; j0 < n; j0 += TB_NB) {
+        const int nbj = n - j0 < TB_NB ? n - j0 : TB_NB;
+        const int r0 = j0 + nbj, nrest = n - r0;
+        double* Ajj = A + (size_t)j0 + (size_t)j0 * lda;
+        potf2_trtri<<<1, TRTRI_THREADS, TRTRI_SMEM, st>>>(nbj, lower, Ajj, lda, inv, j0, dev_info);
+        if (cudaGetLastError() != cudaSuccess) return PB2_ERR_CUDA;
+        if (nrest == 0) break;
+        int rc;
+        if (lower) {  // L21 = A21 inv(L11)^T, then A22 -= L21 L21^T
+            double* A21 = A + (size_t)r0 + (size_t)j0 * lda;
+            rc = parsec_b200_dgemm_sm100('N', 'T', nrest, nbj, nbj, 1.0, A21, lda, inv, TB_NB, 0.0, W, ldw, stream);
+            if (rc != PB2_SUCCESS) return rc;
+            if (cudaMemcpy2DAsync(A21, (size_t)lda * 8, W, (size_t)ldw * 8, (size_t)nrest * 8, nbj, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+                return PB2_ERR_CUDA;
+            rc = parsec_b200_dsyrk_sm100('L', 'N', nrest, nbj, -1.0, W, ldw, 1.0, A + (size_t)r0 + (size_t)r0 * lda, lda, stream);
+        } else {      // U12 = inv(U11)^T A12, then A22 -= U12^T U12
+            double* A12 = A + (size_t)j0 + (size_t)r0 * lda;
+            rc = parsec_b200_dgemm_sm100('T', 'N', nbj, nrest, nbj, 1.0, inv, TB_NB, A12, lda, 0.0, W, TB_NB, stream);
+            if (rc != PB2_SUCCESS) return rc;
+            if (cudaMemcpy2DAsync(A12, (size_t)lda * 8, W, (size_t)TB_NB * 8, (size_t)nbj * 8, nrest, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+                return PB2_ERR_CUDA;
+            rc = parsec_b200_dsyrk_sm100('U', 'T', nrest, nbj, -1.0, W, TB_NB, 1.0, A + (size_t)r0 + (size_t)r0 * lda, lda, stream);
+        }
+        if (rc != PB2_SUCCESS) return rc;
+    }
+    return cudaGetLastError() == cudaSuccess ? PB2_SUCCESS : PB2_ERR_CUDA;
+}
+
+extern "C" int parsec_b200_dpotrf(char uplo, int n, double* A, int lda, void* workspace, size_t workspace_bytes, int* dev_info,
+                                   void* stream) {
+    return parsec_b200_dpotrf_sm100(uplo, n, A, lda, workspace, workspace_bytes, dev_info, stream);
+}

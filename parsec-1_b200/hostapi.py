@@ -85,6 +85,8 @@ def lib():
         "parsec_b200_dgemm_sm100": (i32, [C.c_char, C.c_char, i32, i32, i32, dbl, vp, i32, vp, i32, dbl, vp, i32, vp]),
         "parsec_b200_dsyrk_sm100": (i32, [C.c_char, C.c_char, i32, i32, dbl, vp, i32, dbl, vp, i32, vp]),
         "parsec_b200_dtrsm_workspace": (C.c_size_t, [C.c_char, i32, i32]),
+        "parsec_b200_dpotrf_workspace": (C.c_size_t, [i32]),
+        "parsec_b200_dpotrf_sm100": (i32, [C.c_char, i32, vp, i32, vp, C.c_size_t, vp, vp]),
         "parsec_b200_dtrtri_diag_sm100": (i32, [C.c_char, C.c_char, i32, vp, i32, vp, vp]),
         "parsec_b200_dtrsm_inv_sm100": (i32, [C.c_char, C.c_char, C.c_char, i32, i32, dbl, vp, i32, vp, vp, i32, vp,
                                               C.c_size_t, vp]),

@@ -134,6 +134,50 @@ def test_dtrsm_against_scipy(side, uplo, trans, diag, m, n):
     assert np.array_equal(read_back(dB2, m, n, ldb), X)
 
 
+@pytest.mark.parametrize("uplo", ["L", "U"])
+@pytest.mark.parametrize("n,pad", [(1024, 0), (1000, 2), (130, 0), (128, 4), (64, 0), (5, 1), (2048, 0)])
+def test_dpotrf_tile_on_the_gpu(uplo, n, pad):
+    import torch
+    rng = np.random.default_rng(n + ord(uplo))
+    G = rng.uniform(-0.5, 0.5, (n, n))
+    A = G + G.T + n * np.eye(n)                                   # symmetric, strictly diagonally dominant
+    other = rng.uniform(5.0, 9.0, (n, n))                         # what sits in the triangle that is not referenced
+    stored = (np.tril(A) + np.triu(other, 1)) if uplo == "L" else (np.triu(A) + np.tril(other, -1))
+    lda = n + pad
+    dA, pA = dev_colmajor(stored, lda)
+    L = H.lib()
+    ws_bytes = L.parsec_b200_dpotrf_workspace(n)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    assert L.parsec_b200_dpotrf_sm100(uplo.encode(), n, pA, lda, ws.data_ptr(), ws_bytes, info.data_ptr(),
+                                      torch.cuda.current_stream().cuda_stream) == 0
+    torch.cuda.synchronize()
+    assert info.item() == 0
+    got = read_back(dA, n, n, lda)
+    F = np.tril(got) if uplo == "L" else np.triu(got).T           # the lower factor either way
+    untouched = (lambda X: np.triu(X, 1)) if uplo == "L" else (lambda X: np.tril(X, -1))
+    assert np.array_equal(untouched(got), untouched(stored))
+    assert inf(A - F @ F.T) / (inf(A) * n * EPS) < 10             # LAPACK's test ratio
+    ref = np.linalg.cholesky(A)
+    assert inf(F - ref) / (inf(ref) * np.linalg.cond(A, np.inf) * n * EPS) < 10
+
+
+def test_dpotrf_reports_the_first_bad_pivot():
+    import torch
+    n = 300
+    A = np.eye(n) * 4.0
+    A[200, 200] = -1.0                                            # not positive definite from pivot 201 on
+    dA, pA = dev_colmajor(A, n)
+    L = H.lib()
+    ws_bytes = L.parsec_b200_dpotrf_workspace(n)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    assert L.parsec_b200_dpotrf_sm100(b"L", n, pA, n, ws.data_ptr(), ws_bytes, info.data_ptr(), 0) == 0
+    torch.cuda.synchronize()
+    assert info.item() == 201
+    assert L.parsec_b200_dpotrf_sm100(b"L", n, pA, n, ws.data_ptr(), 100, info.data_ptr(), 0) == -4
+
+
 def test_bad_arguments():
     import torch
     x = torch.zeros(1 << 16, dtype=torch.float64, device="cuda")
@@ -160,7 +204,16 @@ def test_speed_of_the_cholesky_bodies():
         Cm = torch.zeros(n, n, dtype=torch.float64, device="cuda")
         ws_bytes = H.dtrsm_workspace("R", n, n)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
-        calls = {"gemm NT": lambda: H.dgemm("N", "T", n, n, n, -1.0, A.data_ptr(), n, A.data_ptr(), n, 1.0, Cm.data_ptr(), n, s),
+        pws_bytes = H.lib().parsec_b200_dpotrf_workspace(n)
+        pws = torch.empty(pws_bytes, dtype=torch.uint8, device="cuda")
+        P = (A @ A.T + n * torch.eye(n, dtype=torch.float64, device="cuda")).contiguous()
+        P0 = P.clone()
+
+        def potrf():
+            P.copy_(P0)
+            return H.lib().parsec_b200_dpotrf_sm100(b"L", n, P.data_ptr(), n, pws.data_ptr(), pws_bytes, None, s)
+
+        calls = {"potrf L (+ copy)": potrf, "gemm NT": lambda: H.dgemm("N", "T", n, n, n, -1.0, A.data_ptr(), n, A.data_ptr(), n, 1.0, Cm.data_ptr(), n, s),
                  "syrk L": lambda: H.dsyrk("L", "N", n, n, -1.0, A.data_ptr(), n, 1.0, Cm.data_ptr(), n, s),
                  "trsm RLTN": lambda: H.dtrsm("R", "L", "T", "N", n, n, 1.0, T.data_ptr(), n, Cm.data_ptr(), n, ws.data_ptr(), ws_bytes, s)}
         for name, fn in calls.items():
