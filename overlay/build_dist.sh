@@ -59,4 +59,13 @@ gcc -O3 -fopenmp -ffp-contract=off $INC -c "$A/dgemm_NN.c" -o "$A/dgemm_NN.o"
 gcc -O3 -fopenmp -ffp-contract=off $INC -I"$A" -c "$A/dgemm_main.c" -o "$A/dgemm_main.o"
 gcc -fopenmp "$A/dgemm_main.o" "$A/dgemm_NN.o" -o "$OUT/bin/dgemm_NN_dist" -L"$OUT/dist" -l:libparsec.so.4 -lpb2mpi \
     -L/usr/local/cuda/lib64 -lcublas -lcudart -lm -lpthread -ldl -Wl,-rpath-link,"$REPO/parsec-1_b200"
+# the Cholesky application on several ranks
+cp "$REPO/overlay/apps/dpotrf_L.jdf" "$REPO/overlay/apps/dpotrf_main.c" "$A/"
+( cd "$A" && "$B/parsec/interfaces/ptg/ptg-compiler/parsec-ptgpp" -E -i dpotrf_L.jdf -o dpotrf_L -f dpotrf_L > ptgpp_potrf.log 2>&1 ) \
+    || { cat "$A/ptgpp_potrf.log" >&2; exit 5; }
+gcc -O3 -fopenmp $INC -c "$A/dpotrf_L.c" -o "$A/dpotrf_L.o"
+gcc -O3 -fopenmp $INC -I"$A" -c "$A/dpotrf_main.c" -o "$A/dpotrf_main.o"
+gcc -fopenmp "$A/dpotrf_main.o" "$A/dpotrf_L.o" -o "$OUT/bin/dpotrf_L_dist" -L"$OUT/dist" -l:libparsec.so.4 -lpb2mpi \
+    -L"$REPO/parsec-1_b200" -lparsec_b200 -L/usr/local/cuda/lib64 -lcudart -lm -lpthread -ldl \
+    -Wl,-rpath,'$ORIGIN/../../../parsec-1_b200'
 echo "installed:"; ls -la "$OUT/dist" "$OUT/bin/dgemm_NN_dist" "$OUT/reftests/dtd_test_ce" 2>/dev/null || true

@@ -113,3 +113,24 @@ def test_reference_comm_engine_test_runs_over_the_new_engine():
         assert out.count("[0] In callback for tag 3, message sent from 1 size: 8 message: [9.500000,19.500000]") == 2
         assert "[1] GET is over, message:\n[0,1,2,3,4,5,6,7,8]" in out and "[0] Notification of GET over received" in out
         assert "[1] PUT is over, message:\n[0,2,4,6,8,10,12,14,16]" in out and "[0] PUT is finished" in out
+
+
+@pytest.mark.parametrize("P,Q,N,NB", [(2, 2, 768, 128), (1, 3, 1000, 192), (2, 1, 512, 64)])
+def test_cholesky_on_a_grid_of_ranks(tmp_path, P, Q, N, NB):
+    """A DAG with more kinds of remote edges than the GEMM: the factored diagonal tile goes down its panel, every panel
+    tile goes to one SYRK and to the GEMMs of a whole row and a whole column of the trailing matrix -- several
+    destinations per activation, forwarded along the reference's own propagation trees."""
+    from test_overlay_potrf import check_factor
+    exe = os.path.join(REF, "bin", "dpotrf_L_dist")
+    if not os.path.exists(exe):
+        pytest.skip("baseline/_ref/bin/dpotrf_L_dist is not built")
+    n = P * Q
+    dump = str(tmp_path / "L.bin")
+    rc, out, err = run_ranks(n, [exe, "-N", str(N), "-t", str(NB), "-c", "2", "-P", str(P), "-Q", str(Q), "--dump", dump,
+                                 "--", "--mca", "device_cuda_enabled", "0"])
+    assert rc == 0, (rc, out[-1500:], err[-3000:])
+    lines = [json.loads(l) for l in out.splitlines() if l.startswith("{")]
+    assert sorted(l["rank"] for l in lines) == list(range(n))
+    total = {k: sum(l[k] for l in lines) for k in lines[0] if k not in ("rank", "world", "N", "NB", "cores", "gpus", "seconds", "gflops")}
+    check_factor(total, dump, N, NB, gpu=False)
+    assert sum(1 for l in lines if l["trsm_cpu"] + l["syrk_cpu"] + l["gemm_cpu"] + l["potrf"] > 0) == n   # every rank worked
