@@ -23,6 +23,83 @@ constexpr int TB_LD = TB_NB + 1;                // padded shared-memory row
 constexpr int TRTRI_THREADS = 256;
 constexpr size_t TRTRI_SMEM = ((size_t)TB_NB * TB_LD + 8 * 16 * 17) * sizeof(double);
 
+// The lower triangular 128 x 128 matrix in S (row-major, row length TB_LD, zeros above the diagonal) is replaced by its
+// inverse.  All TRTRI_THREADS threads of the CTA; X0 is scratch for the 16 x 16 stage.  In the doubling steps a thread
+// owns four neighbouring outputs of a row, so the four sums run as independent chains off one load of the left factor.
+__device__ __forceinline__ void invert_lower_in_smem(double* S, double* X0, int tid) {
+    if (tid < TB_NB) {  // the eight 16 x 16 diagonal sub-blocks: sub-block b, column c
+        const int b = tid >> 4, c = tid & 15;
+        const double* L = S + (b * 16) * TB_LD + b * 16;
+        double x[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] = 0.0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (i == c) x[i] = 1.0 / L[i * TB_LD + i];
+            if (i > c) {
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if (k < i) acc = fma(L[i * TB_LD + k], x[k], acc);  // x[k] = 0 for k < c
+                x[i] = -acc / L[i * TB_LD + i];
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) X0[(b * 16 + i) * 17 + c] = x[i];
+    }
+    __syncthreads();
+    for (int e = tid; e < 8 * 256; e += TRTRI_THREADS) {
+        const int b = e >> 8, i = (e >> 4) & 15, c = e & 15;
+        S[(b * 16 + i) * TB_LD + b * 16 + c] = X0[(b * 16 + i) * 17 + c];
+    }
+    __syncthreads();
+    for (int sz = 16; sz < TB_NB; sz *= 2) {  // pairs of inverted sz x sz blocks -> inverted 2sz x 2sz blocks
+        const int quads = (TB_NB / (2 * sz)) * sz * (sz / 4);
+        for (int o = tid; o < quads; o += TRTRI_THREADS) {  // tmp = C A^-1, parked in the mirror block
+            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            const double* Crow = S + (base + sz + i) * TB_LD + base;
+            const double* Ainv = S + base * TB_LD + base;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+            for (int k = j; k < sz; ++k) {  // A^-1 is lower triangular: its entries above the diagonal are stored zeros
+                const double c = Crow[k];
+                const double* ar = Ainv + k * TB_LD + j;
+                a0 = fma(c, ar[0], a0);
+                a1 = fma(c, ar[1], a1);
+                a2 = fma(c, ar[2], a2);
+                a3 = fma(c, ar[3], a3);
+            }
+            double* out = S + (base + i) * TB_LD + base + sz + j;
+            out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+        }
+        __syncthreads();
+        for (int o = tid; o < quads; o += TRTRI_THREADS) {  // C = -B^-1 tmp
+            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
+            const double* tmp = S + base * TB_LD + base + sz + j;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+            for (int k = 0; k <= i; ++k) {
+                const double bv = Brow[k];
+                const double* tr = tmp + k * TB_LD;
+                a0 = fma(bv, tr[0], a0);
+                a1 = fma(bv, tr[1], a1);
+                a2 = fma(bv, tr[2], a2);
+                a3 = fma(bv, tr[3], a3);
+            }
+            double* out = S + (base + sz + i) * TB_LD + base + j;
+            out[0] = -a0; out[1] = -a1; out[2] = -a2; out[3] = -a3;
+        }
+        __syncthreads();
+        for (int o = tid; o < quads; o += TRTRI_THREADS) {
+            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            double* out = S + (base + i) * TB_LD + base + sz + j;
+            out[0] = out[1] = out[2] = out[3] = 0.0;
+        }
+        __syncthreads();
+    }
+}
+
 // Inverse of each diagonal block of the triangular matrix T (n x n, `lower` says which triangle is stored), written as
 // full 128 x 128 blocks (ld 128) with zeros in the other triangle.  One CTA per block, all in shared memory:
 //   1. the eight 16 x 16 diagonal sub-blocks by substitution (one thread per column: 16 short dependent steps);
@@ -51,50 +128,7 @@ __global__ void __launch_bounds__(TRTRI_THREADS) trtri_diag_blocks(int n, int lo
         if (lower) S[r * TB_LD + c] = v; else S[c * TB_LD + r] = v;
     }
     __syncthreads();
-    if (tid < TB_NB) {  // 1. sub-block b, column c
-        const int b = tid >> 4, c = tid & 15;
-        const double* L = S + (b * 16) * TB_LD + b * 16;
-        double* x = X0 + (b * 16) * 17 + c;
-        for (int i = 0; i < c; ++i) x[i * 17] = 0.0;
-        x[c * 17] = 1.0 / L[c * TB_LD + c];
-        for (int i = c + 1; i < 16; ++i) {
-            double acc = 0.0;
-            for (int k = c; k < i; ++k) acc = fma(L[i * TB_LD + k], x[k * 17], acc);
-            x[i * 17] = -acc / L[i * TB_LD + i];
-        }
-    }
-    __syncthreads();
-    for (int e = tid; e < 8 * 256; e += TRTRI_THREADS) {
-        const int b = e >> 8, i = (e >> 4) & 15, c = e & 15;
-        S[(b * 16 + i) * TB_LD + b * 16 + c] = X0[(b * 16 + i) * 17 + c];
-    }
-    __syncthreads();
-    for (int sz = 16; sz < TB_NB; sz *= 2) {  // 2. pairs of inverted sz x sz blocks -> inverted 2sz x 2sz blocks
-        const int outputs = (TB_NB / (2 * sz)) * sz * sz;
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {   // tmp = C A^-1, parked in the mirror block
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            const double* Crow = S + (base + sz + i) * TB_LD + base;
-            const double* Ainv = S + base * TB_LD + base;
-            double acc = 0.0;
-            for (int k = j; k < sz; ++k) acc = fma(Crow[k], Ainv[k * TB_LD + j], acc);
-            S[(base + i) * TB_LD + base + sz + j] = acc;
-        }
-        __syncthreads();
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {   // C = -B^-1 tmp
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
-            const double* tmp = S + base * TB_LD + base + sz;
-            double acc = 0.0;
-            for (int k = 0; k <= i; ++k) acc = fma(Brow[k], tmp[k * TB_LD + j], acc);
-            S[(base + sz + i) * TB_LD + base + j] = -acc;
-        }
-        __syncthreads();
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            S[(base + i) * TB_LD + base + sz + j] = 0.0;
-        }
-        __syncthreads();
-    }
+    invert_lower_in_smem(S, X0, tid);
     double* out = Tinv + (size_t)blk * TB_NB * TB_NB;
     for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
         const int r = e % TB_NB, c = e / TB_NB;
@@ -274,28 +308,70 @@ __global__ void __launch_bounds__(TRTRI_THREADS) potf2_trtri(int nb, int lower, 
         if (lower) S[r * TB_LD + c] = v; else S[c * TB_LD + r] = v;
     }
     __syncthreads();
-    for (int j = 0; j < nb; ++j) {
-        const int i = tid;
-        double s = 0.0;
-        if (i >= j && i < nb) {
-            double s0 = 0.0, s1 = 0.0;
-            int k = 0;
-            for (; k + 1 < j; k += 2) {
-                s0 = fma(S[i * TB_LD + k], S[j * TB_LD + k], s0);
-                s1 = fma(S[i * TB_LD + k + 1], S[j * TB_LD + k + 1], s1);
-            }
-            if (k < j) s0 = fma(S[i * TB_LD + k], S[j * TB_LD + k], s0);
-            s = S[i * TB_LD + j] - (s0 + s1);
-            if (i == j) {
-                if (!(s > 0.0)) {
-                    if (!bad) bad = j + 1;
-                    s = 1.0;  // keep going with something finite; the caller reads info
+    // Right-looking, register blocked: the 128 x 128 block is a 16 x 16 grid of 8 x 8 sub-blocks, thread (ti, tj) keeps
+    // sub-block (ti, tj) in registers for the whole factorisation.  Step j: the owner of the diagonal sub-block takes the
+    // square root, the owners of block column j/8 scale their piece of column j and publish it (shared memory, two
+    // buffers in turn), and everybody applies the rank-1 update to its own registers: two barriers and 64 independent
+    // multiply-adds per step, nothing read-modify-written in shared memory.
+    {
+        const int ti = tid & 15, tj = tid >> 4;
+        double* colj = X0;            // 2 x 128 doubles
+        double* dsh = X0 + 2 * TB_NB;  // the pivot of the step
+        double a[8][8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) a[r][c] = S[(8 * ti + r) * TB_LD + 8 * tj + c];
+        for (int jb = 0; jb < 16; ++jb) {
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) {
+                const int j = 8 * jb + jj;
+                double* col = colj + (j & 1) * TB_NB;
+                if (ti == jb && tj == jb) {
+                    double d = a[jj][jj];
+                    if (!(d > 0.0)) {
+                        if (!bad && j < nb) bad = j + 1;
+                        d = 1.0;  // keep going with something finite; the caller reads info
+                    }
+                    d = sqrt(d);
+                    a[jj][jj] = d;
+                    *dsh = d;
                 }
-                S[j * TB_LD + j] = sqrt(s);
+                __syncthreads();
+                if (tj == jb && ti >= jb) {
+                    const double d = *dsh;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        if (ti > jb || r > jj) {
+                            a[r][jj] /= d;
+                            col[8 * ti + r] = a[r][jj];
+                        }
+                    }
+                }
+                __syncthreads();
+                if (ti >= tj && tj >= jb) {
+                    double li[8], lc[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) li[r] = col[8 * ti + r];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) lc[c] = col[8 * tj + c];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        if (tj > jb || c > jj) {   // columns to the right of j only
+#pragma unroll
+                            for (int r = 0; r < 8; ++r)
+                                if (ti > tj || r >= c) a[r][c] = fma(-li[r], lc[c], a[r][c]);   // lower triangle only
+                        }
+                    }
+                }
             }
         }
         __syncthreads();
-        if (i > j && i < nb) S[i * TB_LD + j] = s / S[j * TB_LD + j];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                if (ti > tj || (ti == tj && r >= c)) S[(8 * ti + r) * TB_LD + 8 * tj + c] = a[r][c];
         __syncthreads();
     }
     if (tid == 0 && bad && info && *info == 0) *info = j0 + bad;
@@ -304,51 +380,7 @@ __global__ void __launch_bounds__(TRTRI_THREADS) potf2_trtri(int nb, int lower, 
         if (r < nb && c < nb && (lower ? r >= c : r <= c)) A[(size_t)r + (size_t)c * lda] = lower ? S[r * TB_LD + c] : S[c * TB_LD + r];
     }
     __syncthreads();
-    // the inverse of the factor: same steps as trtri_diag_blocks
-    if (tid < TB_NB) {
-        const int b = tid >> 4, c = tid & 15;
-        const double* L = S + (b * 16) * TB_LD + b * 16;
-        double* x = X0 + (b * 16) * 17 + c;
-        for (int i = 0; i < c; ++i) x[i * 17] = 0.0;
-        x[c * 17] = 1.0 / L[c * TB_LD + c];
-        for (int i = c + 1; i < 16; ++i) {
-            double acc = 0.0;
-            for (int k = c; k < i; ++k) acc = fma(L[i * TB_LD + k], x[k * 17], acc);
-            x[i * 17] = -acc / L[i * TB_LD + i];
-        }
-    }
-    __syncthreads();
-    for (int e = tid; e < 8 * 256; e += TRTRI_THREADS) {
-        const int b = e >> 8, i = (e >> 4) & 15, c = e & 15;
-        S[(b * 16 + i) * TB_LD + b * 16 + c] = X0[(b * 16 + i) * 17 + c];
-    }
-    __syncthreads();
-    for (int sz = 16; sz < TB_NB; sz *= 2) {
-        const int outputs = (TB_NB / (2 * sz)) * sz * sz;
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            const double* Crow = S + (base + sz + i) * TB_LD + base;
-            const double* Ainv = S + base * TB_LD + base;
-            double acc = 0.0;
-            for (int k = j; k < sz; ++k) acc = fma(Crow[k], Ainv[k * TB_LD + j], acc);
-            S[(base + i) * TB_LD + base + sz + j] = acc;
-        }
-        __syncthreads();
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
-            const double* tmp = S + base * TB_LD + base + sz;
-            double acc = 0.0;
-            for (int k = 0; k <= i; ++k) acc = fma(Brow[k], tmp[k * TB_LD + j], acc);
-            S[(base + sz + i) * TB_LD + base + j] = -acc;
-        }
-        __syncthreads();
-        for (int o = tid; o < outputs; o += TRTRI_THREADS) {
-            const int j = o % sz, i = (o / sz) % sz, base = (o / (sz * sz)) * 2 * sz;
-            S[(base + i) * TB_LD + base + sz + j] = 0.0;
-        }
-        __syncthreads();
-    }
+    invert_lower_in_smem(S, X0, tid);  // the inverse of the factor
     for (int e = tid; e < TB_NB * TB_NB; e += TRTRI_THREADS) {
         const int r = e % TB_NB, c = e / TB_NB;
         inv[e] = lower ? S[r * TB_LD + c] : S[c * TB_LD + r];
