@@ -462,15 +462,21 @@ __device__ __forceinline__ void dgemm_tile_tma(const CUtensorMap* mapA_p, const 
                     }
                 }
             } else {
+                // element by element (ragged rows, unaligned C, or the diagonal block of a triangular update); the old
+                // values of the column are all requested before the first store, one L2 round trip instead of eight
+                double oldv[8];
+                bool ok[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int row = row_of(i);
-                    if (TRI == 1 && row < col) continue;  // diagonal block of a triangular update
-                    if (TRI == 2 && row > col) continue;
-                    if (row < M) {
-                        double* cptr = C + (size_t)row + (size_t)col * ldc;
-                        *cptr = beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, *cptr) : __dmul_rn(alpha, acc[i][j][e]);
-                    }
+                    ok[i] = row < M && !(TRI == 1 && row < col) && !(TRI == 2 && row > col);
+                    oldv[i] = (ok[i] && beta != 0.0) ? C[(size_t)row + (size_t)col * ldc] : 0.0;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (ok[i])
+                        C[(size_t)row_of(i) + (size_t)col * ldc] =
+                            beta != 0.0 ? axpby(alpha, acc[i][j][e], beta, oldv[i]) : __dmul_rn(alpha, acc[i][j][e]);
                 }
             }
         }

@@ -25,7 +25,9 @@ constexpr size_t TRTRI_SMEM = ((size_t)TB_NB * TB_LD + 8 * 16 * 17) * sizeof(dou
 
 // The lower triangular 128 x 128 matrix in S (row-major, row length TB_LD, zeros above the diagonal) is replaced by its
 // inverse.  All TRTRI_THREADS threads of the CTA; X0 is scratch for the 16 x 16 stage.  In the doubling steps a thread
-// owns four neighbouring outputs of a row, so the four sums run as independent chains off one load of the left factor.
+// owns four neighbouring outputs of a row, so the four sums run as independent chains off one load of the left factor;
+// the lanes of a warp take different ROWS: their loads of the left factor are TB_LD apart (no bank conflict) and their
+// loads of the right factor are one address (broadcast).
 __device__ __forceinline__ void invert_lower_in_smem(double* S, double* X0, int tid) {
     if (tid < TB_NB) {  // the eight 16 x 16 diagonal sub-blocks: sub-block b, column c
         const int b = tid >> 4, c = tid & 15;
@@ -56,7 +58,7 @@ __device__ __forceinline__ void invert_lower_in_smem(double* S, double* X0, int 
     for (int sz = 16; sz < TB_NB; sz *= 2) {  // pairs of inverted sz x sz blocks -> inverted 2sz x 2sz blocks
         const int quads = (TB_NB / (2 * sz)) * sz * (sz / 4);
         for (int o = tid; o < quads; o += TRTRI_THREADS) {  // tmp = C A^-1, parked in the mirror block
-            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            const int i = o % sz, j = ((o / sz) % (sz / 4)) * 4, base = (o / (sz * (sz / 4))) * 2 * sz;
             const double* Crow = S + (base + sz + i) * TB_LD + base;
             const double* Ainv = S + base * TB_LD + base;
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
@@ -74,7 +76,7 @@ __device__ __forceinline__ void invert_lower_in_smem(double* S, double* X0, int 
         }
         __syncthreads();
         for (int o = tid; o < quads; o += TRTRI_THREADS) {  // C = -B^-1 tmp
-            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            const int i = o % sz, j = ((o / sz) % (sz / 4)) * 4, base = (o / (sz * (sz / 4))) * 2 * sz;
             const double* Brow = S + (base + sz + i) * TB_LD + base + sz;
             const double* tmp = S + base * TB_LD + base + sz + j;
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
@@ -92,7 +94,7 @@ __device__ __forceinline__ void invert_lower_in_smem(double* S, double* X0, int 
         }
         __syncthreads();
         for (int o = tid; o < quads; o += TRTRI_THREADS) {
-            const int j = (o % (sz / 4)) * 4, i = (o / (sz / 4)) % sz, base = (o / (sz * (sz / 4))) * 2 * sz;
+            const int i = o % sz, j = ((o / sz) % (sz / 4)) * 4, base = (o / (sz * (sz / 4))) * 2 * sz;
             double* out = S + (base + i) * TB_LD + base + sz + j;
             out[0] = out[1] = out[2] = out[3] = 0.0;
         }
@@ -344,7 +346,7 @@ __global__ void __launch_bounds__(TRTRI_THREADS) potf2_trtri(int nb, int lower, 
                     for (int r = 0; r < 8; ++r) {
                         if (ti > jb || r > jj) {
                             a[r][jj] /= d;
-                            col[8 * ti + r] = a[r][jj];
+                            col[16 * r + ti] = a[r][jj];   /* row 8 ti + r, stored r-major: lanes differ in ti */
                         }
                     }
                 }
@@ -352,9 +354,9 @@ __global__ void __launch_bounds__(TRTRI_THREADS) potf2_trtri(int nb, int lower, 
                 if (ti >= tj && tj >= jb) {
                     double li[8], lc[8];
 #pragma unroll
-                    for (int r = 0; r < 8; ++r) li[r] = col[8 * ti + r];
+                    for (int r = 0; r < 8; ++r) li[r] = col[16 * r + ti];
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) lc[c] = col[8 * tj + c];
+                    for (int c = 0; c < 8; ++c) lc[c] = col[16 * c + tj];
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
                         if (tj > jb || c > jj) {   // columns to the right of j only
