@@ -6,7 +6,7 @@
 #   overlay/device_cuda_b200_shim.c in place of the CUDA module, as in the single-rank overlay
 #   libpb2mpi.so (overlay/pb2mpi) as "the MPI" CMake finds: datatypes + the few communicator calls, no point-to-point
 #   dist/libparsec.so.4, dist/libpb2mpi.so, bin/dgemm_NN_dist (the same JDF and driver, PARSEC_HAVE_MPI defined),
-#   reftests/dtd_test_ce (the reference's own comm-engine test, unmodified source)
+#   reftests/dtd_test_ce (the reference's own comm-engine test) and reftests/dist/* (its multi-rank tests), unmodified
 # Ranks are started by overlay/pb2run.  The single-rank trees (build_overlay.sh) are not touched.
 set -euo pipefail
 REPO="$(cd "$(dirname "$0")/.." && pwd)"
@@ -45,9 +45,21 @@ mkdir -p "$B"
 cp -L "$B/parsec/libparsec.so.4" "$OUT/dist/libparsec.so.4"
 grep -q "PARSEC_HAVE_MPI" "$B/parsec/include/parsec/parsec_options.h" || { echo "the dist tree was configured without MPI" >&2; exit 4; }
 
-# 4. the reference's own comm-engine test, unmodified (tests/dsl/dtd/dtd_test_ce.c)
+# 4. the reference's own comm-engine test and its multi-rank tests, unmodified sources (run by overlay/run_dist_reftests.sh)
 ( cd "$B" && ninja -j"$JOBS" dtd_test_ce > ninja_dtd_test_ce.log 2>&1 ) && cp "$B/tests/dsl/dtd/dtd_test_ce" "$OUT/reftests/dtd_test_ce" \
     || echo "reference test dtd_test_ce did not build (see $B/ninja_dtd_test_ce.log)" >&2
+mkdir -p "$OUT/reftests/dist"
+for t in dtd_test_pingpong dtd_test_task_inserting_task dtd_test_task_insertion dtd_test_war dtd_test_interleave_actions \
+         dtd_test_allreduce dtd_test_new_tile jdf_forward_RW_NULL jdf_forward_READ_NULL write_check compose project merge_sort \
+         reshape input_dep_reshape_single_copy remote_multiple_outs_same_pred_flow testing_redistribute \
+         testing_redistribute_random testing_band testing_stencil_1D bw_test schedmicro rtt; do
+    if ( cd "$B" && ninja -j"$JOBS" $t > ninja_$t.log 2>&1 ); then
+        f=$(cd "$B" && find tests -type f -name $t -perm -u+x | head -1)
+        [ -n "$f" ] && cp "$B/$f" "$OUT/reftests/dist/$t"
+    else
+        echo "reference test $t did not build (see $B/ninja_$t.log)" >&2
+    fi
+done
 
 # 5. the application, against this tree's headers (PARSEC_HAVE_MPI and DISTRIBUTED come from them)
 A="$WORK/app_dist"

@@ -102,6 +102,8 @@ typedef struct {
 #define MPI_AINT 27
 #define MPI_LB 28 /* MPI-1 markers, only as members of MPI_Type_struct */
 #define MPI_UB 29
+#define MPI_2INT 30
+#define MPI_DOUBLE_INT 31
 #define PB2MPI_FIRST_DERIVED 64
 
 #define MPI_COMBINER_NAMED 1
@@ -117,6 +119,13 @@ typedef struct {
 #define MPI_MAX 1
 #define MPI_MIN 2
 #define MPI_SUM 3
+#define MPI_MAXLOC 4
+#define MPI_MINLOC 5
+#define MPI_PROD 6
+#define MPI_LAND 7
+#define MPI_LOR 8
+#define MPI_BAND 9
+#define MPI_BOR 10
 
 #define MPI_TAG_UB 1
 #define MPI_ERRORS_RETURN 1
@@ -149,6 +158,8 @@ int MPI_Barrier(MPI_Comm comm);
 int MPI_Allreduce(const void* sendbuf, void* recvbuf, int count, MPI_Datatype type, MPI_Op op, MPI_Comm comm);
 int MPI_Reduce(const void* sendbuf, void* recvbuf, int count, MPI_Datatype type, MPI_Op op, int root, MPI_Comm comm);
 int MPI_Bcast(void* buf, int count, MPI_Datatype type, int root, MPI_Comm comm);
+int MPI_Allgather(const void* sendbuf, int sendcount, MPI_Datatype sendtype, void* recvbuf, int recvcount,
+                  MPI_Datatype recvtype, MPI_Comm comm);
 int MPI_Gather(const void* sendbuf, int sendcount, MPI_Datatype sendtype, void* recvbuf, int recvcount,
                MPI_Datatype recvtype, int root, MPI_Comm comm);
 int MPI_Gatherv(const void* sendbuf, int sendcount, MPI_Datatype sendtype, void* recvbuf, const int* recvcounts,

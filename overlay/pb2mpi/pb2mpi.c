@@ -39,7 +39,8 @@ static const struct { int size; const char *name; } predefined[PB2MPI_FIRST_DERI
     [MPI_INT64_T] = {8, "MPI_INT64_T"}, [MPI_UINT8_T] = {1, "MPI_UINT8_T"}, [MPI_UINT16_T] = {2, "MPI_UINT16_T"},
     [MPI_UINT32_T] = {4, "MPI_UINT32_T"}, [MPI_UINT64_T] = {8, "MPI_UINT64_T"}, [MPI_C_COMPLEX] = {8, "MPI_C_COMPLEX"},
     [MPI_C_DOUBLE_COMPLEX] = {16, "MPI_C_DOUBLE_COMPLEX"}, [MPI_AINT] = {sizeof(MPI_Aint), "MPI_AINT"},
-    [MPI_LB] = {0, "MPI_LB"}, [MPI_UB] = {0, "MPI_UB"},
+    [MPI_LB] = {0, "MPI_LB"}, [MPI_UB] = {0, "MPI_UB"}, [MPI_2INT] = {8, "MPI_2INT"},
+    [MPI_DOUBLE_INT] = {16, "MPI_DOUBLE_INT"},
 };
 
 #define MAX_TYPES 4096
@@ -442,7 +443,9 @@ int MPI_Init_thread(int *argc, char ***argv, int required, int *provided)
             return MPI_ERR_OTHER;
         }
     }
-    thread_level = required > MPI_THREAD_SERIALIZED ? MPI_THREAD_SERIALIZED : required;   /* one comm thread at a time */
+    /* MPI_THREAD_MULTIPLE can be granted: the collectives here work on the job's shared segment, not on the rings, and
+     * pb2_ce_send takes a lock per destination; only polling is for one thread (the comm thread of the runtime) */
+    thread_level = required > MPI_THREAD_MULTIPLE ? MPI_THREAD_MULTIPLE : required;
     if( provided ) *provided = thread_level;
     initialized = 1;
     return MPI_SUCCESS;
@@ -549,25 +552,71 @@ int MPI_Barrier(MPI_Comm comm)
     return PB2_SUCCESS == pb2_ce_barrier(transport) ? MPI_SUCCESS : MPI_ERR_OTHER;
 }
 
-static int as_i64(const void *buf, int i, MPI_Datatype type, int64_t *v)
+/* every rank's `bytes` bytes, ordered by rank, into all (world_size * bytes); 128 bytes per rank per round */
+static int allgather_bytes(const void *mine, size_t bytes, void *all)
 {
+    char *rounds = (char*)malloc((size_t)world_size * 128);
+    for( size_t done = 0; done < bytes; done += 128 ) {
+        const size_t n = bytes - done < 128 ? bytes - done : 128;
+        char piece[128] = {0};
+        memcpy(piece, (const char*)mine + done, n);
+        if( PB2_SUCCESS != pb2_ce_allgather(transport, piece, 128, rounds) ) { free(rounds); return MPI_ERR_OTHER; }
+        for( int r = 0; r < world_size; r++ ) memcpy((char*)all + (size_t)r * bytes + done, rounds + (size_t)r * 128, n);
+    }
+    free(rounds);
+    return MPI_SUCCESS;
+}
+
+#define REDUCE_LOOP(T) do { T *o = (T*)out; const T *x = (const T*)in; for( int i = 0; i < count; i++ ) {                \
+        switch( op ) { case MPI_MAX: if( x[i] > o[i] ) o[i] = x[i]; break; case MPI_MIN: if( x[i] < o[i] ) o[i] = x[i]; break; \
+                       case MPI_SUM: o[i] += x[i]; break; case MPI_PROD: o[i] *= x[i]; break;                              \
+                       case MPI_LAND: o[i] = (T)(o[i] && x[i]); break; case MPI_LOR: o[i] = (T)(o[i] || x[i]); break;    \
+                       default: return 0; } } return 1; } while(0)
+#define REDUCE_BITS(T) do { T *o = (T*)out; const T *x = (const T*)in; for( int i = 0; i < count; i++ ) {                \
+        if( MPI_BAND == op ) o[i] &= x[i]; else o[i] |= x[i]; } return 1; } while(0)
+
+/* out = out (op) in, element by element; 0 when the pair (type, op) is not served */
+static int reduce_into(void *out, const void *in, int count, MPI_Datatype type, MPI_Op op)
+{
+    if( MPI_MAXLOC == op || MPI_MINLOC == op ) {
+        if( MPI_2INT == type ) {
+            int *o = (int*)out; const int *x = (const int*)in;
+            for( int i = 0; i < count; i++ )
+                if( (MPI_MAXLOC == op ? x[2*i] > o[2*i] : x[2*i] < o[2*i]) || (x[2*i] == o[2*i] && x[2*i+1] < o[2*i+1]) ) { o[2*i] = x[2*i]; o[2*i+1] = x[2*i+1]; }
+            return 1;
+        }
+        if( MPI_DOUBLE_INT == type ) {
+            struct di { double v; int i; };
+            struct di *o = (struct di*)out; const struct di *x = (const struct di*)in;
+            for( int i = 0; i < count; i++ )
+                if( (MPI_MAXLOC == op ? x[i].v > o[i].v : x[i].v < o[i].v) || (x[i].v == o[i].v && x[i].i < o[i].i) ) o[i] = x[i];
+            return 1;
+        }
+        return 0;
+    }
+    if( MPI_BAND == op || MPI_BOR == op ) {
+        switch( type ) {
+        case MPI_INT: case MPI_INT32_T: case MPI_UNSIGNED: case MPI_UINT32_T: REDUCE_BITS(uint32_t);
+        case MPI_LONG: case MPI_LONG_LONG: case MPI_INT64_T: case MPI_UNSIGNED_LONG: case MPI_UNSIGNED_LONG_LONG: case MPI_UINT64_T: REDUCE_BITS(uint64_t);
+        case MPI_CHAR: case MPI_BYTE: case MPI_UNSIGNED_CHAR: case MPI_UINT8_T: case MPI_INT8_T: REDUCE_BITS(uint8_t);
+        default: return 0;
+        }
+    }
     switch( type ) {
-    case MPI_INT: case MPI_INT32_T: *v = ((const int32_t*)buf)[i]; return 1;
-    case MPI_UNSIGNED: case MPI_UINT32_T: *v = ((const uint32_t*)buf)[i]; return 1;
-    case MPI_LONG: case MPI_LONG_LONG: case MPI_INT64_T: case MPI_AINT: *v = ((const int64_t*)buf)[i]; return 1;
-    case MPI_UNSIGNED_LONG: case MPI_UNSIGNED_LONG_LONG: case MPI_UINT64_T: *v = (int64_t)((const uint64_t*)buf)[i]; return 1;
+    case MPI_INT: case MPI_INT32_T: REDUCE_LOOP(int32_t);
+    case MPI_UNSIGNED: case MPI_UINT32_T: REDUCE_LOOP(uint32_t);
+    case MPI_LONG: case MPI_LONG_LONG: case MPI_INT64_T: case MPI_AINT: REDUCE_LOOP(int64_t);
+    case MPI_UNSIGNED_LONG: case MPI_UNSIGNED_LONG_LONG: case MPI_UINT64_T: REDUCE_LOOP(uint64_t);
+    case MPI_SHORT: case MPI_INT16_T: REDUCE_LOOP(int16_t);
+    case MPI_CHAR: case MPI_SIGNED_CHAR: case MPI_INT8_T: REDUCE_LOOP(int8_t);
+    case MPI_UNSIGNED_CHAR: case MPI_BYTE: case MPI_UINT8_T: REDUCE_LOOP(uint8_t);
+    case MPI_FLOAT: REDUCE_LOOP(float);
+    case MPI_DOUBLE: REDUCE_LOOP(double);
     default: return 0;
     }
 }
-static void from_i64(void *buf, int i, MPI_Datatype type, int64_t v)
-{
-    switch( type ) {
-    case MPI_INT: case MPI_INT32_T: ((int32_t*)buf)[i] = (int32_t)v; break;
-    case MPI_UNSIGNED: case MPI_UINT32_T: ((uint32_t*)buf)[i] = (uint32_t)v; break;
-    default: ((int64_t*)buf)[i] = v; break;
-    }
-}
 
+/* every rank gathers every contribution and reduces them in rank order: all ranks get the same bits */
 int MPI_Allreduce(const void *sendbuf, void *recvbuf, int count, MPI_Datatype type, MPI_Op op, MPI_Comm comm)
 {
     int size;
@@ -577,16 +626,35 @@ int MPI_Allreduce(const void *sendbuf, void *recvbuf, int count, MPI_Datatype ty
         if( in != recvbuf ) memcpy(recvbuf, in, (size_t)count * size);
         return MPI_SUCCESS;
     }
-    const int pb2_op = MPI_MAX == op ? 0 : MPI_SUM == op ? 1 : MPI_MIN == op ? 2 : -1;
-    if( pb2_op < 0 ) return MPI_ERR_ARG;
-    for( int done = 0; done < count; done += 16 ) {   /* integers only: all the runtime reduces is a taskpool id */
-        int64_t v[16];
-        int n = count - done < 16 ? count - done : 16;
-        for( int i = 0; i < n; i++ ) if( !as_i64(in, done + i, type, &v[i]) ) return MPI_ERR_ARG;
-        if( PB2_SUCCESS != pb2_ce_allreduce_i64(transport, v, n, pb2_op) ) return MPI_ERR_OTHER;
-        for( int i = 0; i < n; i++ ) from_i64(recvbuf, done + i, type, v[i]);
+    const size_t bytes = (size_t)count * size;
+    if( 0 == bytes ) return MPI_Barrier(comm);
+    char *all = (char*)malloc((size_t)world_size * bytes);
+    int rc = allgather_bytes(in, bytes, all);
+    if( MPI_SUCCESS == rc ) {
+        memcpy(recvbuf, all, bytes);
+        for( int r = 1; r < world_size && MPI_SUCCESS == rc; r++ )
+            if( !reduce_into(recvbuf, all + (size_t)r * bytes, count, type, op) ) rc = MPI_ERR_ARG;
     }
-    return MPI_SUCCESS;
+    free(all);
+    return rc;
+}
+
+int MPI_Allgather(const void *sendbuf, int sendcount, MPI_Datatype sendtype, void *recvbuf, int recvcount,
+                  MPI_Datatype recvtype, MPI_Comm comm)
+{
+    int size, rank;
+    (void)recvcount; (void)recvtype;
+    if( MPI_SUCCESS != MPI_Type_size(sendtype, &size) || sendcount < 0 ) return MPI_ERR_ARG;
+    MPI_Comm_rank(comm, &rank);
+    const size_t bytes = (size_t)sendcount * size;
+    const void *in = (MPI_IN_PLACE == sendbuf) ? (const char*)recvbuf + (size_t)rank * bytes : sendbuf;
+    if( comm_is_self(comm) || NULL == transport ) { if( in != recvbuf ) memcpy(recvbuf, in, bytes); return MPI_SUCCESS; }
+    if( 0 == bytes ) return MPI_Barrier(comm);
+    char *mine = (char*)malloc(bytes);
+    memcpy(mine, in, bytes);
+    int rc = allgather_bytes(mine, bytes, recvbuf);
+    free(mine);
+    return rc;
 }
 
 int MPI_Reduce(const void *sendbuf, void *recvbuf, int count, MPI_Datatype type, MPI_Op op, int root, MPI_Comm comm)
