@@ -31,6 +31,8 @@
 #include <mpi.h>
 #include <pthread.h>
 #include <stdlib.h>
+#include <stdio.h>
+#include <time.h>
 #include <string.h>
 
 #include "parsec_b200.h"
@@ -113,6 +115,16 @@ static int b200_nb_ops = 0, b200_waiting_gets = 0;
 static b200_parked_t *b200_parked_head = NULL, *b200_parked_tail = NULL;
 static pthread_mutex_t b200_parked_lock = PTHREAD_MUTEX_INITIALIZER;
 static int b200_events = 0;    /* counted by the dispatch below, reported by progress() */
+
+/* PB2_CE_STATS=1: where the engine's time goes, printed by every rank when the engine shuts down */
+static struct { uint64_t puts, put_bytes, put_ns, regs, ams, am_bytes, progress_calls, cb_ns; } b200_st;
+static int b200_stats_on = 0;
+static inline uint64_t b200_now_ns(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+}
 
 /* ---- layouts ---- */
 /* pieces of `count` elements of `datatype` at `base` (+displ); returns the number of pieces, -1 when out of memory */
@@ -285,6 +297,7 @@ static int b200_mem_register(void *mem, parsec_mem_type_t mem_type, size_t count
             r->blocklen = (int64_t)r->bytes;
         }
     }
+    b200_st.regs++;
     *lreg = (parsec_ce_mem_reg_handle_t)r;
     if( NULL != lreg_size ) *lreg_size = B200_REG_PUBLIC;
     return PARSEC_SUCCESS;
@@ -411,7 +424,11 @@ static void b200_run_op(b200_op_t *op)
         }
         nl = b200_local_iov(op->lreg, op->ldispl, &lv);
         nr = b200_remote_iov(peer, op->rdispl, &rv);
-        rc = (nl < 0 || nr < 0) ? PB2_ERR_OUT_OF_RESOURCE : pb2_ce_put(b200_tp, op->remote, lv, nl, rv, nr);
+        {
+            const uint64_t t0 = b200_stats_on ? b200_now_ns() : 0;
+            rc = (nl < 0 || nr < 0) ? PB2_ERR_OUT_OF_RESOURCE : pb2_ce_put(b200_tp, op->remote, lv, nl, rv, nr);
+            if( b200_stats_on ) { b200_st.put_ns += b200_now_ns() - t0; b200_st.puts++; b200_st.put_bytes += op->lreg->bytes; }
+        }
         free(lv);
         free(rv);
         if( PB2_SUCCESS != rc )
@@ -437,12 +454,16 @@ static void b200_dispatch(void *user, int src, uint64_t tag, const void *msg, si
 {
     (void)user;
     b200_events++;
+    b200_st.ams++;
+    b200_st.am_bytes += len;
     if( tag < B200_MAX_TAGS ) {
         if( NULL == b200_tags[tag].cb ) {
             parsec_warning("comm engine: message with unregistered tag %llu from rank %d dropped", (unsigned long long)tag, src);
             return;
         }
+        const uint64_t t0 = b200_stats_on ? b200_now_ns() : 0;
         b200_tags[tag].cb(&parsec_ce, tag, (void*)msg, len, src, b200_tags[tag].cb_data);
+        if( b200_stats_on ) b200_st.cb_ns += b200_now_ns() - t0;
         return;
     }
     if( B200_TAG_PUT_DONE == tag ) {
@@ -511,6 +532,7 @@ static int b200_progress(parsec_comm_engine_t *ce)
 {
     (void)ce;
     if( NULL == b200_tp ) return 0;
+    b200_st.progress_calls++;
     int n = b200_flush_parked();
     b200_events = 0;
     pb2_ce_poll(b200_tp, b200_dispatch, NULL, 0);
@@ -573,6 +595,7 @@ parsec_comm_engine_t *parsec_comm_engine_init(parsec_context_t *context)
         return NULL;
     }
     if( b200_up ) { parsec_ce.parsec_context = context; return &parsec_ce; }
+    { const char *e = getenv("PB2_CE_STATS"); b200_stats_on = (NULL != e && atoi(e)); }
     MPI_Comm_rank(MPI_COMM_WORLD, &b200_rank);
     MPI_Comm_size(MPI_COMM_WORLD, &b200_world);
     b200_tp = (pb2_ce_t*)PB2MPI_Transport();   /* NULL in a world of one: nothing to talk to */
@@ -616,6 +639,13 @@ int parsec_comm_engine_fini(parsec_comm_engine_t *ce)
     /* what is still queued goes out before the tags disappear */
     for( int spin = 0; spin < 1000 && (NULL != b200_parked_head || NULL != b200_ops_head); spin++ ) b200_progress(ce);
     if( NULL != b200_tp ) pb2_ce_set_wait_poll(b200_tp, NULL, NULL);
+    if( b200_stats_on )
+        fprintf(stderr, "[comm engine, rank %d] puts %llu (%.1f MiB, %.2f ms in the copies = %.2f GB/s), registrations %llu, "
+                "active messages in %llu (%.1f KiB, %.2f ms in their callbacks), progress calls %llu\n",
+                b200_rank, (unsigned long long)b200_st.puts, b200_st.put_bytes / 1048576.0, b200_st.put_ns * 1e-6,
+                b200_st.put_ns ? (double)b200_st.put_bytes / (double)b200_st.put_ns : 0.0, (unsigned long long)b200_st.regs,
+                (unsigned long long)b200_st.ams, b200_st.am_bytes / 1024.0, b200_st.cb_ns * 1e-6,
+                (unsigned long long)b200_st.progress_calls);
     memset(b200_tags, 0, sizeof(b200_tags));
     if( NULL != ce->parsec_context ) ce->parsec_context->comm_ctx = -1;   /* as the MPI engine leaves it (:601-604) */
     b200_tp = NULL;   /* the transport belongs to MPI_Finalize */
