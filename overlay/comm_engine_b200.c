@@ -92,6 +92,7 @@ typedef struct b200_op_s {
     uint32_t cb_size;
     char cb_data[B200_MAX_CB_DATA];
     uint64_t peer_op;          /* kind 2: which get of the peer this answers */
+    int status;                /* of the transfer, when a copier thread made it */
 } b200_op_t;
 
 typedef struct b200_parked_s {
@@ -409,28 +410,19 @@ static void b200_send_done(int dst, uint64_t r_tag, uint64_t target_self, const 
     b200_send_or_park(dst, B200_TAG_PUT_DONE, &m, offsetof(b200_done_msg_t, cb_data) + cb_size);
 }
 
+static int b200_copy_now(b200_op_t *op);
+static int b200_offload_put(b200_op_t *op);
+static int b200_first_put_done;
+
 static void b200_run_op(b200_op_t *op)
 {
     const b200_reg_t *peer = (const b200_reg_t*)op->rreg;
-    pb2_ce_iov_t *lv = NULL, *rv = NULL;
-    int nl, nr, rc;
+    int rc;
     switch( op->kind ) {
     case 0:   /* put: ours -> theirs, then their callback, then ours */
     case 2:   /* the same on behalf of the peer's get: the reply finishes it over there */
-        if( NULL != op->lreg->bounce ) {   /* refresh the packed image of what we send */
-            int pos = 0;
-            MPI_Pack((void*)(uintptr_t)op->lreg->mem, op->lreg->count, op->lreg->datatype, op->lreg->bounce,
-                     (int)op->lreg->bytes, &pos, MPI_COMM_WORLD);
-        }
-        nl = b200_local_iov(op->lreg, op->ldispl, &lv);
-        nr = b200_remote_iov(peer, op->rdispl, &rv);
-        {
-            const uint64_t t0 = b200_stats_on ? b200_now_ns() : 0;
-            rc = (nl < 0 || nr < 0) ? PB2_ERR_OUT_OF_RESOURCE : pb2_ce_put(b200_tp, op->remote, lv, nl, rv, nr);
-            if( b200_stats_on ) { b200_st.put_ns += b200_now_ns() - t0; b200_st.puts++; b200_st.put_bytes += op->lreg->bytes; }
-        }
-        free(lv);
-        free(rv);
+        rc = b200_copy_now(op);
+        b200_first_put_done = 1;
         if( PB2_SUCCESS != rc )
             parsec_fatal("comm engine: put of %llu bytes to rank %d failed (%d)", (unsigned long long)op->lreg->bytes, op->remote, rc);
         if( 0 == op->kind ) {
@@ -448,6 +440,127 @@ static void b200_run_op(b200_op_t *op)
         free(op);
         break;
     }
+}
+
+/* ---- copier threads ----
+ * A put of a tile is a copy of megabytes by whoever executes it; done by the communication thread it stops that
+ * thread from answering anybody for as long (the MPI engine hands the same work to MPI_Isend and goes on).  Large
+ * puts can therefore be handed to a few copier threads (PB2_CE_COPY_THREADS = 1 .. 8; default 0 = none, because the
+ * gain has only been looked at in a container whose memory system saturates with one copying thread): a copier builds the
+ * piece lists, makes the one-copy transfer, sends the completion record to the target, and gives the operation back;
+ * the origin's callback still runs on the communication thread, from progress().  Only on the one-copy path: puts
+ * staged through the rings need this rank's polling, which belongs to the communication thread. */
+#define B200_COPY_MIN_BYTES (256u * 1024u)
+static pthread_mutex_t b200_copy_lock = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t b200_copy_cond = PTHREAD_COND_INITIALIZER;
+static b200_op_t *b200_copy_head = NULL, *b200_copy_tail = NULL;      /* waiting for a copier */
+static b200_op_t *b200_copied_head = NULL, *b200_copied_tail = NULL;  /* copied, callback not run yet */
+static pthread_t b200_copiers[8];
+static int b200_nb_copiers = 0, b200_copiers_wanted = -1, b200_copy_inflight = 0, b200_copy_stop = 0, b200_first_put_done = 0;
+
+static int b200_copy_now(b200_op_t *op)   /* the transfer itself; any thread */
+{
+    const b200_reg_t *peer = (const b200_reg_t*)op->rreg;
+    pb2_ce_iov_t *lv = NULL, *rv = NULL;
+    if( NULL != op->lreg->bounce ) {   /* refresh the packed image of what we send */
+        int pos = 0;
+        MPI_Pack((void*)(uintptr_t)op->lreg->mem, op->lreg->count, op->lreg->datatype, op->lreg->bounce,
+                 (int)op->lreg->bytes, &pos, MPI_COMM_WORLD);
+    }
+    int nl = b200_local_iov(op->lreg, op->ldispl, &lv), nr = b200_remote_iov(peer, op->rdispl, &rv);
+    const uint64_t t0 = b200_stats_on ? b200_now_ns() : 0;
+    int rc = (nl < 0 || nr < 0) ? PB2_ERR_OUT_OF_RESOURCE : pb2_ce_put(b200_tp, op->remote, lv, nl, rv, nr);
+    if( b200_stats_on ) {
+        __atomic_fetch_add(&b200_st.put_ns, b200_now_ns() - t0, __ATOMIC_RELAXED);
+        __atomic_fetch_add(&b200_st.puts, 1, __ATOMIC_RELAXED);
+        __atomic_fetch_add(&b200_st.put_bytes, op->lreg->bytes, __ATOMIC_RELAXED);
+    }
+    free(lv);
+    free(rv);
+    return rc;
+}
+
+static void *b200_copier_main(void *arg)
+{
+    (void)arg;
+    for( ;; ) {
+        pthread_mutex_lock(&b200_copy_lock);
+        while( NULL == b200_copy_head && !b200_copy_stop ) pthread_cond_wait(&b200_copy_cond, &b200_copy_lock);
+        b200_op_t *op = b200_copy_head;
+        if( NULL == op ) { pthread_mutex_unlock(&b200_copy_lock); return NULL; }
+        b200_copy_head = op->next;
+        if( NULL == b200_copy_head ) b200_copy_tail = NULL;
+        pthread_mutex_unlock(&b200_copy_lock);
+        op->next = NULL;
+        op->status = b200_copy_now(op);
+        if( PB2_SUCCESS == op->status )   /* the target may run its callback from now on; ours waits for progress() */
+            b200_send_done(op->remote, op->r_tag, (uint64_t)(uintptr_t)((const b200_reg_t*)op->rreg)->self, op->cb_data, op->cb_size);
+        pthread_mutex_lock(&b200_copy_lock);
+        if( NULL == b200_copied_tail ) b200_copied_head = op; else b200_copied_tail->next = op;
+        b200_copied_tail = op;
+        pthread_mutex_unlock(&b200_copy_lock);
+    }
+}
+
+/* communication thread: hand a put to the copiers; 0 when it has to be done here */
+static int b200_offload_put(b200_op_t *op)
+{
+    if( b200_copiers_wanted < 0 ) {
+        const char *e = getenv("PB2_CE_COPY_THREADS");
+        b200_copiers_wanted = (NULL != e) ? atoi(e) : 0;
+        if( b200_copiers_wanted > 8 ) b200_copiers_wanted = 8;
+    }
+    if( b200_copiers_wanted <= 0 || 0 != op->kind || op->lreg->bytes < B200_COPY_MIN_BYTES || op->remote == b200_rank ) return 0;
+    if( !b200_first_put_done ) return 0;   /* the first put, done here, finds out whether this box allows one-copy puts */
+    pb2_ce_stats_t st;
+    pb2_ce_stats(b200_tp, &st);
+    if( !st.single_copy ) return 0;
+    while( b200_nb_copiers < b200_copiers_wanted ) {
+        if( 0 != pthread_create(&b200_copiers[b200_nb_copiers], NULL, b200_copier_main, NULL) ) { b200_copiers_wanted = b200_nb_copiers; break; }
+        b200_nb_copiers++;
+    }
+    if( 0 == b200_nb_copiers ) return 0;
+    pthread_mutex_lock(&b200_copy_lock);
+    op->next = NULL;
+    if( NULL == b200_copy_tail ) b200_copy_head = op; else b200_copy_tail->next = op;
+    b200_copy_tail = op;
+    b200_copy_inflight++;
+    pthread_cond_signal(&b200_copy_cond);
+    pthread_mutex_unlock(&b200_copy_lock);
+    return 1;
+}
+
+/* communication thread: run the callbacks of the puts the copiers have finished */
+static int b200_reap_copied(void)
+{
+    if( 0 == b200_copy_inflight ) return 0;
+    pthread_mutex_lock(&b200_copy_lock);
+    b200_op_t *op = b200_copied_head;
+    b200_copied_head = b200_copied_tail = NULL;
+    pthread_mutex_unlock(&b200_copy_lock);
+    int n = 0;
+    while( NULL != op ) {
+        b200_op_t *next = op->next;
+        if( PB2_SUCCESS != op->status )
+            parsec_fatal("comm engine: put of %llu bytes to rank %d failed (%d)", (unsigned long long)op->lreg->bytes, op->remote, op->status);
+        b200_finish_local(op, 0);
+        free(op);
+        b200_copy_inflight--;
+        n++;
+        op = next;
+    }
+    return n;
+}
+
+static void b200_stop_copiers(void)
+{
+    pthread_mutex_lock(&b200_copy_lock);
+    b200_copy_stop = 1;
+    pthread_cond_broadcast(&b200_copy_cond);
+    pthread_mutex_unlock(&b200_copy_lock);
+    for( int i = 0; i < b200_nb_copiers; i++ ) pthread_join(b200_copiers[i], NULL);
+    b200_nb_copiers = 0;
+    b200_copy_stop = 0;
 }
 
 static void b200_dispatch(void *user, int src, uint64_t tag, const void *msg, size_t len)
@@ -495,7 +608,10 @@ static int b200_progress_ops(void)
         op->next = NULL;
         b200_nb_ops--;
         done++;
-        if( 1 != op->kind ) { b200_run_op(op); continue; }
+        if( 1 != op->kind ) {
+            if( !b200_offload_put(op) ) b200_run_op(op);   /* a large put goes to a copier thread */
+            continue;
+        }
         /* get */
         const b200_reg_t *peer = (const b200_reg_t*)op->rreg;
         pb2_ce_stats_t st;
@@ -538,6 +654,7 @@ static int b200_progress(parsec_comm_engine_t *ce)
     pb2_ce_poll(b200_tp, b200_dispatch, NULL, 0);
     n += b200_events;
     n += b200_progress_ops();
+    n += b200_reap_copied();
     return n;
 }
 
@@ -582,7 +699,7 @@ static int b200_sync(parsec_comm_engine_t *ce)
 static int b200_can_serve(parsec_comm_engine_t *ce)
 {
     (void)ce;
-    return b200_nb_ops + b200_waiting_gets < 64;
+    return b200_nb_ops + b200_waiting_gets + b200_copy_inflight < 64;
 }
 
 /* ---- the seam ---- */
@@ -638,6 +755,8 @@ int parsec_comm_engine_fini(parsec_comm_engine_t *ce)
     if( !b200_up ) return 1;
     /* what is still queued goes out before the tags disappear */
     for( int spin = 0; spin < 1000 && (NULL != b200_parked_head || NULL != b200_ops_head); spin++ ) b200_progress(ce);
+    while( b200_copy_inflight > 0 ) b200_progress(ce);   /* the copiers finish what they hold */
+    b200_stop_copiers();
     if( NULL != b200_tp ) pb2_ce_set_wait_poll(b200_tp, NULL, NULL);
     if( b200_stats_on )
         fprintf(stderr, "[comm engine, rank %d] puts %llu (%.1f MiB, %.2f ms in the copies = %.2f GB/s), registrations %llu, "

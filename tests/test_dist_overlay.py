@@ -91,6 +91,15 @@ def test_the_same_run_with_puts_staged_through_the_rings(tmp_path):
     check(lines, dump, 1024, 256, 2, 2)
 
 
+def test_puts_handed_to_copier_threads(tmp_path):
+    """PB2_CE_COPY_THREADS=3: tiles are copied by helper threads while the communication thread keeps answering; the
+    completion of each put still reaches the runtime on the communication thread."""
+    _need()
+    dump = str(tmp_path / "C.bin")
+    lines = run_gemm(4, 2, 2, 2048, 256, dump, env_extra={"PB2_CE_COPY_THREADS": "3"})
+    check(lines, dump, 2048, 256, 2, 2)
+
+
 def test_small_rings_make_the_engine_park_and_resume_messages(tmp_path):
     """64 KiB rings (the smallest that hold the longest activation message the runtime registers, 4 x 4 KiB + header):
     activations and tile pieces pile up faster than the peer drains them; the engine parks messages and keeps order."""
