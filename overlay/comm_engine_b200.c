@@ -30,6 +30,7 @@
 
 #include <mpi.h>
 #include <pthread.h>
+#include <sched.h>
 #include <stdlib.h>
 #include <stdio.h>
 #include <time.h>
@@ -713,6 +714,18 @@ parsec_comm_engine_t *parsec_comm_engine_init(parsec_context_t *context)
     }
     if( b200_up ) { parsec_ce.parsec_context = context; return &parsec_ce; }
     { const char *e = getenv("PB2_CE_STATS"); b200_stats_on = (NULL != e && atoi(e)); }
+    {   /* This runs on the communication thread, which a runtime built without hwloc has just pinned to core number
+         * nb_workers -- the same core for every rank of the box (remote_dep.c:688-699).  A launcher that has given
+         * this rank its own cores says so in PB2_CE_CORES=lo-hi, and the thread goes back to them. */
+        const char *e = getenv("PB2_CE_CORES");
+        int lo = -1, hi = -1;
+        if( NULL != e && 2 == sscanf(e, "%d-%d", &lo, &hi) && lo >= 0 && hi >= lo && hi < CPU_SETSIZE ) {
+            cpu_set_t mask;
+            CPU_ZERO(&mask);
+            for( int c = lo; c <= hi; c++ ) CPU_SET(c, &mask);
+            (void)sched_setaffinity(0, sizeof(mask), &mask);
+        }
+    }
     MPI_Comm_rank(MPI_COMM_WORLD, &b200_rank);
     MPI_Comm_size(MPI_COMM_WORLD, &b200_world);
     b200_tp = (pb2_ce_t*)PB2MPI_Transport();   /* NULL in a world of one: nothing to talk to */

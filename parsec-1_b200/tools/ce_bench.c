@@ -85,12 +85,49 @@ int main(void)
         pb2_ce_barrier(ce);
         gbs[b] = (double)blocks[b] * reps / (now() - t1) * 1e-9;
     }
+    /* the same 8 MiB put, but never twice from or to the same memory: 32 source and 32 target tiles in turn (256 MiB
+     * each side, far more than the caches hold), which is what a runtime moving distinct tiles does */
+    double cold_gbs = 0.0, cold_memcpy_gbs = 0.0;
+    {
+        const size_t tile = 8u << 20, ntiles = 32;
+        char *big = (char*)malloc(tile * ntiles);
+        memset(big, rank + 3, tile * ntiles);
+        uint64_t mine2 = (uint64_t)(uintptr_t)big;
+        got = 0;
+        send_all(ce, peer, 2, &mine2, 8);
+        wait_for(ce, 1);
+        pb2_ce_barrier(ce);
+        double t1 = now();
+        if( 0 == rank ) {
+            for( int rep = 0; rep < 4; rep++ )
+                for( size_t i = 0; i < ntiles; i++ ) {
+                    pb2_ce_iov_t l = {big + i * tile, tile}, r = {(void*)(uintptr_t)(peer_addr + ((i * 7) % ntiles) * tile), tile};
+                    if( PB2_SUCCESS != pb2_ce_put(ce, peer, &l, 1, &r, 1) ) return 2;
+                }
+            send_all(ce, peer, 1, buf, 8);
+        } else {
+            got = 0;
+            wait_for(ce, 1);
+        }
+        pb2_ce_barrier(ce);
+        cold_gbs = (double)tile * ntiles * 4 / (now() - t1) * 1e-9;
+        char *other = (char*)malloc(tile * ntiles);
+        memset(other, 1, tile * ntiles);
+        pb2_ce_barrier(ce);
+        t1 = now();
+        if( 0 == rank ) for( size_t i = 0; i < ntiles; i++ ) memcpy(other + ((i * 7) % ntiles) * tile, big + i * tile, tile);
+        cold_memcpy_gbs = (double)tile * ntiles / (now() - t1) * 1e-9;
+        pb2_ce_barrier(ce);
+        free(other);
+        free(big);
+    }
     pb2_ce_stats_t st;
     pb2_ce_stats(ce, &st);
     if( 0 == rank )
         printf("{\"am_half_rtt_us_8B\": %.3f, \"am_half_rtt_us_1KiB\": %.3f, \"am_rate_Mmsg_s_64B\": %.2f, "
-               "\"put_GBs_1MiB\": %.2f, \"put_GBs_8MiB\": %.2f, \"put_GBs_32MiB\": %.2f, \"single_copy\": %d}\n",
-               lat[0], lat[1], rate, gbs[0], gbs[1], gbs[2], st.single_copy);
+               "\"put_GBs_1MiB\": %.2f, \"put_GBs_8MiB\": %.2f, \"put_GBs_32MiB\": %.2f, "
+               "\"put_GBs_8MiB_distinct_tiles\": %.2f, \"memcpy_GBs_8MiB_distinct_tiles\": %.2f, \"single_copy\": %d}\n",
+               lat[0], lat[1], rate, gbs[0], gbs[1], gbs[2], cold_gbs, cold_memcpy_gbs, st.single_copy);
     pb2_ce_barrier(ce);
     pb2_ce_detach(ce);
     if( child ) { int status; waitpid(child, &status, 0); }
