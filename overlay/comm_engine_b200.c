@@ -446,8 +446,8 @@ static void b200_run_op(b200_op_t *op)
 /* ---- copier threads ----
  * A put of a tile is a copy of megabytes by whoever executes it; done by the communication thread it stops that
  * thread from answering anybody for as long (the MPI engine hands the same work to MPI_Isend and goes on).  Large
- * puts can therefore be handed to a few copier threads (PB2_CE_COPY_THREADS = 1 .. 8; default 0 = none, because the
- * gain has only been looked at in a container whose memory system saturates with one copying thread): a copier builds the
+ * puts are therefore handed to a few copier threads (PB2_CE_COPY_THREADS = 0 .. 8, default 2; on the B200 box's host
+ * two of them take a two-rank GEMM from 0.37 to 0.20 s per run, profiles/comm_shm_r2.md): a copier builds the
  * piece lists, makes the one-copy transfer, sends the completion record to the target, and gives the operation back;
  * the origin's callback still runs on the communication thread, from progress().  Only on the one-copy path: puts
  * staged through the rings need this rank's polling, which belongs to the communication thread. */
@@ -508,7 +508,7 @@ static int b200_offload_put(b200_op_t *op)
 {
     if( b200_copiers_wanted < 0 ) {
         const char *e = getenv("PB2_CE_COPY_THREADS");
-        b200_copiers_wanted = (NULL != e) ? atoi(e) : 0;
+        b200_copiers_wanted = (NULL != e) ? atoi(e) : 2;
         if( b200_copiers_wanted > 8 ) b200_copiers_wanted = 8;
     }
     if( b200_copiers_wanted <= 0 || 0 != op->kind || op->lreg->bytes < B200_COPY_MIN_BYTES || op->remote == b200_rank ) return 0;
