@@ -202,3 +202,32 @@ def test_mca_parameter_names_from_the_environment(monkeypatch):
     assert [L.pb2_device_is_enabled(i) for i in range(4)] == [1, 0, 1, 0]
     monkeypatch.setenv("PARSEC_MCA_device_cuda_enabled", "0")
     assert L.pb2_device_is_enabled(0) == 0
+
+
+def test_blas3_entry_points_validate_their_arguments_before_touching_the_gpu():
+    """Argument errors of parsec_b200_dgemm / _dsyrk / _dtrsm / _dpotrf and the scratch sizes are host logic: they answer
+    PB2_ERR_BAD_PARAM (-4) or 0 without a CUDA call, so they can be checked here."""
+    import ctypes as C
+    L = H.lib()
+    p = C.c_void_p(0x1000)                      # never dereferenced on these paths
+    assert H.dgemm("Q", "N", 8, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8) == -4
+    assert H.dgemm("N", "T", 8, 8, 8, 1.0, p, 8, p, 4, 1.0, p, 8) == -4          # op(B) = B^T is stored n x k: ldb >= n
+    assert H.dgemm("T", "N", 8, 8, 16, 1.0, p, 8, p, 16, 1.0, p, 8) == -4        # op(A) = A^T is stored k x m: lda >= k
+    assert H.dgemm("N", "N", 0, 8, 8, 1.0, p, 8, p, 8, 1.0, p, 8) == 0
+    assert H.dsyrk("X", "N", 8, 8, 1.0, p, 8, 1.0, p, 8) == -4
+    assert H.dsyrk("L", "T", 8, 16, 1.0, p, 8, 1.0, p, 8) == -4                   # A is k x n: lda >= k
+    assert H.dsyrk("U", "N", 0, 8, 1.0, p, 8, 1.0, p, 8) == 0
+    # scratch: inverted 128 x 128 diagonal blocks of the triangular tile + one m x n image of the solution
+    assert H.dtrsm_workspace("R", 1024, 1024) == (8 * 128 * 128 + 1024 * 1024) * 8 + 512
+    assert H.dtrsm_workspace("L", 1000, 300) == (8 * 128 * 128 + 1000 * 300) * 8 + 512
+    assert H.dtrsm_workspace("R", 1001, 130) == (2 * 128 * 128 + 1002 * 130) * 8 + 512   # odd m: leading dimension made even
+    assert H.dtrsm_workspace("Z", 8, 8) == 0
+    assert H.dtrsm("R", "L", "T", "N", 8, 8, 1.0, p, 4, p, 8, p, 1 << 20) == -4    # ldt < n
+    assert H.dtrsm("R", "L", "T", "N", 8, 8, 1.0, p, 8, p, 8, p, 16) == -4         # scratch too small
+    assert H.dtrsm("L", "U", "N", "Q", 8, 8, 1.0, p, 8, p, 8, p, 1 << 20) == -4    # diag
+    assert H.dtrsm("L", "U", "N", "U", 0, 8, 1.0, p, 8, p, 8, p, 1 << 20) == 0
+    assert L.parsec_b200_dpotrf_workspace(1024) == (128 * 128 + 1024 * 128) * 8 + 512
+    assert L.parsec_b200_dpotrf_sm100(b"Q", 8, p, 8, p, 1 << 20, None, None) == -4
+    assert L.parsec_b200_dpotrf_sm100(b"L", 8, p, 4, p, 1 << 20, None, None) == -4
+    assert L.parsec_b200_dpotrf_sm100(b"L", 8, p, 8, p, 16, None, None) == -4
+    assert L.parsec_b200_dpotrf_sm100(b"U", 0, p, 8, p, 16, None, None) == 0
