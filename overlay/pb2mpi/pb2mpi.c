@@ -436,7 +436,10 @@ int MPI_Init_thread(int *argc, char ***argv, int required, int *provided)
     if( world_size > 1 ) {
         const char *ring = getenv("PB2_CE_RING_BYTES");
         char name[96];
-        snprintf(name, sizeof(name), "%s", job ? job : "default");
+        const char *run = getenv("TORCHELASTIC_RUN_ID");   /* torchrun: tells two launches on the same port apart */
+        if( NULL != getenv("PB2_CE_JOB") || NULL == run ) snprintf(name, sizeof(name), "%s", job ? job : "default");
+        else snprintf(name, sizeof(name), "%.40s.%.40s", run, job ? job : "default");
+        for( char *c = name; *c; c++ ) if( '/' == *c ) *c = '_';
         int rc = pb2_ce_attach(name, my_rank, world_size, ring ? (size_t)strtoull(ring, NULL, 0) : 0, &transport);
         if( PB2_SUCCESS != rc ) {
             fprintf(stderr, "pb2mpi: rank %d of %d could not join job '%s' (pb2_ce_attach: %d)\n", my_rank, world_size, name, rc);
