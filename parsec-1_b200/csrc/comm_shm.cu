@@ -150,7 +150,13 @@ extern "C" int pb2_ce_attach(const char* job, int rank, int world, size_t ring_b
     }
     h->pids[rank] = (int32_t)getpid();
     std::atomic_thread_fence(std::memory_order_seq_cst);
-    h->attached.fetch_add(1);
+    if (h->attached.fetch_add(1) >= world) {  // more arrivals than ranks: the segment is what a dead job left behind
+        fprintf(stderr, "pb2_ce_attach: /dev/shm%s belongs to an earlier job of the same name; remove it or pick another name\n",
+                ce->name);
+        munmap(p, ce->seg_bytes);
+        delete ce;
+        return PB2_ERR_BAD_PARAM;
+    }
     const double limit = now_s() + 120.0;
     while (h->attached.load() < world) {  // rendezvous: everybody's pid and rings are in place after this
         if (now_s() > limit || h->failed.load()) {

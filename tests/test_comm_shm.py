@@ -50,3 +50,19 @@ def test_puts_staged_through_the_rings_when_cross_memory_attach_is_refused():
     outs = launch(3, env_extra={"PB2_CE_NO_CMA": "1"})
     for o in outs:
         assert o["single_copy"] == 0 and o["staged_bytes"] >= (64 << 20)
+
+
+def test_a_segment_left_by_a_dead_job_is_refused():
+    """Same job name twice without cleaning up in between (what a crashed launch leaves under /dev/shm): the second
+    job must not mistake the first one's ranks for its own."""
+    import ctypes as C
+    L = C.CDLL(os.path.join(os.path.dirname(HERE), "parsec-1_b200", "libparsec_b200.so"))
+    L.pb2_ce_attach.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]
+    job = ("stale%s" % uuid.uuid4().hex[:10]).encode()
+    ce = C.c_void_p()
+    assert L.pb2_ce_attach(job, 0, 1, 4096, C.byref(ce)) == 0          # a world of one attaches at once ...
+    try:
+        again = C.c_void_p()                                            # ... and never detaches: the segment stays
+        assert L.pb2_ce_attach(job, 0, 1, 4096, C.byref(again)) == -4
+    finally:
+        os.unlink("/dev/shm/pb2ce.%s" % job.decode())
