@@ -67,6 +67,45 @@ def main():
     cb = RECV(on_msg)
     L.pb2_ce_set_wait_poll(ce, cb, None)
 
+    if scenario == "threads":
+        # several threads of a rank send at once (what worker threads do when the runtime runs with
+        # MPI_THREAD_MULTIPLE); one thread polls.  Per (source, thread) the order must hold, nothing may be lost or torn.
+        import threading
+        NT, PER = 4, 800
+        seen = {}
+
+        def on_t(user, src, tag, msg, n):
+            data = C.string_at(msg, n)
+            t, i = int.from_bytes(data[:4], "little"), int.from_bytes(data[4:8], "little")
+            assert data[8:] == bytes([(t * 31 + i) % 251]) * (n - 8), "torn message"
+            assert seen.get((src, t), -1) == i - 1, "order from rank %d thread %d" % (src, t)
+            seen[(src, t)] = i
+
+        cbt = RECV(on_t)
+        stop = threading.Event()
+
+        def sender(t):
+            for i in range(PER):
+                n = 8 + (i * 13 + t * 7) % 900
+                data = t.to_bytes(4, "little") + i.to_bytes(4, "little") + bytes([(t * 31 + i) % 251]) * (n - 8)
+                buf = C.create_string_buffer(data, n)
+                for dst in range(world):
+                    while L.pb2_ce_send(ce, dst, 77, buf, n) != 0:
+                        pass                                   # full: the polling thread drains
+
+        threads = [threading.Thread(target=sender, args=(t,)) for t in range(NT)]
+        for th in threads:
+            th.start()
+        while len(seen) < world * NT or any(v < PER - 1 for v in seen.values()):
+            L.pb2_ce_poll(ce, cbt, None, 0)
+        for th in threads:
+            th.join()
+        assert L.pb2_ce_barrier(ce) == 0
+        L.pb2_ce_set_wait_poll(ce, RECV(0), None)
+        assert L.pb2_ce_detach(ce) == 0
+        print(json.dumps({"rank": rank, "received": world * NT * PER}))
+        return
+
     def send(dst, tag, data):
         buf = C.create_string_buffer(data, len(data)) if data else None
         while True:

@@ -46,6 +46,11 @@ def test_messages_puts_and_collectives_between_processes(world):
             assert o["single_copy"] == 1 and o["staged_bytes"] == 0 and o["put_bytes"] >= (64 << 20)
 
 
+def test_several_threads_of_a_rank_send_at_once():
+    outs = launch(3, scenario="threads")
+    assert all(o["received"] == 3 * 4 * 800 for o in outs)
+
+
 def test_puts_staged_through_the_rings_when_cross_memory_attach_is_refused():
     outs = launch(3, env_extra={"PB2_CE_NO_CMA": "1"})
     for o in outs:

@@ -206,3 +206,45 @@ def test_a_world_of_one_and_handles(M):
     h = C.c_int(t)
     assert M.MPI_Type_free(C.byref(h)) == 0 and h.value == 0
     assert M.MPI_Type_size(t, C.byref(n)) != 0                                             # the handle is gone
+
+
+def test_random_nested_types_against_the_model(M):
+    """Randomly nested constructors (what a user of parsec_type_create_* can build), 60 types: size, bounds, packing,
+    unpacking and the merged layout must all follow the typemap rules of the model above."""
+    rng = np.random.default_rng(20260)
+
+    def build(depth):
+        if depth == 0 or rng.random() < 0.25:
+            t = int(rng.choice([MPI_BYTE, MPI_INT, MPI_DOUBLE]))
+            return t, prim(t)
+        h, m = build(depth - 1)
+        ext = m[2] - m[1]
+        kind = int(rng.integers(0, 5))
+        if kind == 0:
+            n = int(rng.integers(1, 5))
+            return new(M, M.MPI_Type_contiguous, n, h), m_contig(n, m)
+        if kind == 1:
+            c, bl = int(rng.integers(1, 4)), int(rng.integers(1, 4))
+            st = bl + int(rng.integers(0, 4))
+            return new(M, M.MPI_Type_vector, c, bl, st, h), m_vector(c, bl, st, m)
+        if kind == 2:
+            c, bl = int(rng.integers(1, 4)), int(rng.integers(1, 3))
+            st = bl * ext + 8 * int(rng.integers(0, 5))
+            return new(M, M.MPI_Type_create_hvector, c, bl, st, h), m_hvector(c, bl, st, m)
+        if kind == 3:
+            c = int(rng.integers(1, 4))
+            bls = [int(rng.integers(1, 3)) for _ in range(c)]
+            disps, at = [], 0
+            for b in bls:                                   # increasing, non-overlapping displacements
+                at += int(rng.integers(0, 3))
+                disps.append(at)
+                at += b
+            return (new(M, M.MPI_Type_indexed, c, (C.c_int * c)(*bls), (C.c_int * c)(*disps), h), m_indexed(bls, disps, m))
+        pad = 8 * int(rng.integers(0, 4))
+        return new(M, M.MPI_Type_create_resized, h, m[1], ext + pad), m_resized(m, m[1], ext + pad)
+
+    for _ in range(60):
+        handle, model = build(int(rng.integers(1, 4)))
+        if handle < 64:
+            continue
+        check(M, handle, model, count=int(rng.integers(1, 4)))
