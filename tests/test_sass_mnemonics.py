@@ -26,3 +26,29 @@ def test_library_sass_has_the_blackwell_instructions():
                      "SYNCS.ARRIVE.TRANS64",  # mbarrier arrive.expect_tx
                      "USETMAXREG"):           # setmaxnreg in the warp-specialised DGEMM
         assert mnemonic in sass, mnemonic
+
+
+@pytest.mark.skipif(CUOBJDUMP is None, reason="cuobjdump not found")
+def test_every_fp64_tile_kernel_is_the_tma_dmma_code():
+    """The transposed GEMM variants and the SYRK kernels are instantiations of the same tile code as dgemm_nn_tma: each of
+    them must contain the TMA loads, the mbarrier waits and the DMMA instructions, and none of them a local-memory
+    spill loop (a handful of spill instructions at most)."""
+    import re
+    lib = os.path.join(ROOT, "parsec-1_b200", "libparsec_b200.so")
+    sass = subprocess.run([CUOBJDUMP, "-sass", lib], capture_output=True, text=True, timeout=300).stdout
+    functions = {}
+    for chunk in sass.split("Function : ")[1:]:
+        name, _, body = chunk.partition("\n")
+        functions[name.strip()] = body
+    wanted = {"dgemm_nn_tma": 1, "dgemm_tma_trans": 3, "dsyrk_tma": 4, "dgemm_nn_tma_grouped": 2}
+    for stem, count in wanted.items():
+        # nvcc mangles the names as <length><identifier>: anchor on that so that dgemm_nn_tma does not also count the grouped kernel
+        names = [n for n in functions if re.search(r"\d+%s(E|I)" % stem, n)]
+        assert len(names) == count, (stem, names)
+        for n in names:
+            body = functions[n]
+            assert body.count("DMMA.8x8x4") >= 128, n             # 32 per k-step x 4 k-steps per stage, unrolled
+            assert "UTMALDG.2D" in body and "SYNCS.PHASECHK" in body and "USETMAXREG" in body, n
+            assert body.count("STL") + body.count("LDL") <= 12, (n, body.count("STL"), body.count("LDL"))
+    for stem in ("trtri_diag_blocks", "potf2_trtri"):
+        assert any(stem in n for n in functions), stem
